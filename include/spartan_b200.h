@@ -1,0 +1,173 @@
+/*
+ * spartan_b200.h -- C ABI of libspartan_b200.so, the B200-native backend for the
+ * Spartan NIZK prove step that Otti's run.py drives
+ * (run.py:58,100 -> spartan-zkinterface/src/main.rs:57-100 -> libspartan).
+ *
+ * Each entry point replaces one item of libspartan's public Rust API
+ * (/root/reference/Spartan/src/lib.rs); the citation after each declaration is
+ * the reference interface it stands in for.  INTEGRATION.md shows the Rust shim
+ * that binds these symbols and keeps the Instance / Assignment / NIZKGens / NIZK
+ * types unchanged for callers.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no CUDA or torch types cross the boundary;
+ *  - scalars cross as 32-byte canonical little-endian integers < l
+ *    (Scalar::from_bytes, scalar/ristretto255.rs:398-422); a value >= l yields
+ *    SB200_ERR_INVALID_SCALAR exactly where the reference returns
+ *    R1CSError::InvalidScalar;
+ *  - proofs cross as the bincode 1.3 serialisation of the reference's `NIZK`
+ *    struct (lib.rs:481-485), byte-identical to the reference for the same
+ *    instance, assignment, generators, transcript label and tape seed;
+ *  - return value 0 = success, negative = error (codes below); no panic, abort
+ *    or C++ exception crosses the boundary.  sb200_last_error() gives the text
+ *    for the calling thread;
+ *  - there is NO CPU fallback: every compute entry point fails with
+ *    SB200_ERR_NO_DEVICE when no sm_100 GPU is usable.
+ */
+#ifndef SPARTAN_B200_H
+#define SPARTAN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sb200_instance sb200_instance; /* libspartan::Instance      (lib.rs:115-118) */
+typedef struct sb200_gens sb200_gens;         /* libspartan::NIZKGens      (lib.rs:459-462) */
+
+enum {
+  SB200_OK = 0,
+  /* R1CSError, errors.rs:19-32 */
+  SB200_ERR_NON_POW2_CONS = -1,
+  SB200_ERR_NON_POW2_VARS = -2,
+  SB200_ERR_INVALID_NUMBER_OF_INPUTS = -3,
+  SB200_ERR_INVALID_NUMBER_OF_VARS = -4,
+  SB200_ERR_INVALID_SCALAR = -5,
+  SB200_ERR_INVALID_INDEX = -6,
+  /* ProofVerifyError, errors.rs:4-10 (and the reference's verify-side panics) */
+  SB200_ERR_PROOF_VERIFY = -20,
+  SB200_ERR_PROOF_MALFORMED = -21,
+  /* conditions on which the reference panics (assert!) */
+  SB200_ERR_ASSERT = -30,
+  /* backend */
+  SB200_ERR_NO_DEVICE = -100,
+  SB200_ERR_CUDA = -101,
+  SB200_ERR_ARG = -102
+};
+
+/*
+ * Caller-owned Fiat-Shamir transcript (merlin::Transcript keeps its state
+ * private, so the Rust side passes two thunks over its own object; hashing
+ * stays on the host as north_star requires).  NULL selects the library's
+ * built-in Merlin, seeded with Transcript::new(label).
+ *   append_message  == merlin::Transcript::append_message(label, msg)
+ *   challenge_bytes == merlin::Transcript::challenge_bytes(label, out)
+ */
+typedef struct sb200_transcript_vt {
+  void* ctx;
+  void (*append_message)(void* ctx, const uint8_t* label, size_t label_len, const uint8_t* msg, size_t msg_len);
+  void (*challenge_bytes)(void* ctx, const uint8_t* label, size_t label_len, uint8_t* out, size_t out_len);
+} sb200_transcript_vt;
+
+/* merlin::Transcript for callers without their own (C, C++, Python hosts).
+ *   sb200_transcript_new             == Transcript::new(label)                  (spzk main.rs:78)
+ *   sb200_transcript_append_message  == Transcript::append_message
+ *   sb200_transcript_challenge_bytes == Transcript::challenge_bytes
+ *   sb200_transcript_vtable fills a vtable bound to the object, to pass to prove/verify:
+ *   the object's state advances exactly as the reference mutates `&mut Transcript`. */
+typedef struct sb200_transcript sb200_transcript;
+int sb200_transcript_new(const uint8_t* label, size_t label_len, sb200_transcript** out);
+void sb200_transcript_append_message(sb200_transcript* t, const uint8_t* label, size_t label_len, const uint8_t* msg, size_t msg_len);
+void sb200_transcript_challenge_bytes(sb200_transcript* t, const uint8_t* label, size_t label_len, uint8_t* out, size_t out_len);
+void sb200_transcript_vtable(sb200_transcript* t, sb200_transcript_vt* out);
+void sb200_transcript_free(sb200_transcript* t);
+
+/*
+ * Multi-GPU exchange hook (one process per GPU).  The prover shards the
+ * hypercube / commitment rows across `world` ranks and needs only an
+ * all-gather of a few dozen bytes per Fiat-Shamir round; the host side
+ * supplies it (torch.distributed NCCL/gloo from Python, NCCL from Rust).
+ * NULL = single GPU.
+ *   allgather: every rank contributes `bytes` bytes from HOST memory `send`;
+ *   `recv` (HOST, world*bytes) receives the contributions in rank order.
+ */
+typedef struct sb200_comm_vt {
+  void* ctx;
+  int rank;
+  int world;
+  int (*allgather)(void* ctx, const void* send, size_t bytes, void* recv);
+} sb200_comm_vt;
+
+/* Selects the CUDA device for the calling process (one process per GPU).
+ * Fails with SB200_ERR_NO_DEVICE if it is not compute capability 10.x. */
+int sb200_init(int device);
+
+/* Assignment::new(&[[u8;32]]) -> Result<Assignment, R1CSError>            lib.rs:65-89
+ * SB200_ERR_INVALID_SCALAR if any of the n values is not a canonical scalar. */
+int sb200_assignment_check(const uint8_t* vals32, uint64_t n);
+
+/* Instance::new(num_cons, num_vars, num_inputs, &A, &B, &C)              lib.rs:121-225
+ * rows/cols/vals32: three COO matrices; vals32[m] holds nnz[m] x 32 bytes. */
+int sb200_instance_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
+                       const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
+                       sb200_instance** out);
+
+/* Instance::produce_synthetic_r1cs(num_cons, num_vars, num_inputs)       lib.rs:260-271
+ * OsRng is replaced by SplitMix64(seed) so runs are reproducible.  vars32_out
+ * (num_vars x 32 B) and inputs32_out (num_inputs x 32 B) receive the
+ * satisfying assignment. */
+int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t seed,
+                             sb200_instance** out, uint8_t* vars32_out, uint8_t* inputs32_out);
+
+/* Instance::is_sat(&vars, &inputs) -> Result<bool, R1CSError>            lib.rs:228-257 */
+int sb200_instance_is_sat(const sb200_instance* inst, const uint8_t* vars32, uint64_t n_vars, const uint8_t* inputs32,
+                          uint64_t n_inputs, int* sat_out);
+
+/* padded sizes: out[0]=num_cons, out[1]=num_vars, out[2]=num_inputs (r1csinstance.rs:124-134) */
+int sb200_instance_dims(const sb200_instance* inst, uint64_t out[3]);
+void sb200_instance_free(sb200_instance* inst);
+
+/* NIZKGens::new(num_cons, num_vars, num_inputs)                          lib.rs:466-477
+ * label is b"gens_r1cs_sat" in the reference (lib.rs:475); NULL selects it.
+ * Besides deriving the generators this builds the fixed-base window tables in
+ * HBM that the commitment kernel reads (one-off, outside the timed prove, as
+ * the reference builds its gens outside the bench loop, benches/nizk.rs:27-39). */
+int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs,
+                   sb200_gens** out);
+void sb200_gens_free(sb200_gens* gens);
+
+/* NIZK::prove(&inst, vars, &inputs, &gens, &mut transcript) -> NIZK      lib.rs:493-535
+ *  transcript      caller transcript, or NULL to use Transcript::new(label)
+ *  label           transcript label when transcript == NULL (b"nizk_example" in spzk, main.rs:78)
+ *  tape_seed64     64 uniform bytes -> Scalar::from_bytes_wide, standing in for the
+ *                  Scalar::random(OsRng) that seeds RandomTape (random.rs:11-19);
+ *                  NULL draws them from the OS like the reference.
+ *  comm            NULL, or the exchange hook when the proof is sharded over several GPUs
+ *  proof_out/len   bincode(NIZK); release with sb200_free
+ * SB200_ERR_ASSERT where the reference asserts (inputs.len() >= vars.len(), r1csproof.rs:153). */
+int sb200_nizk_prove(const sb200_instance* inst, const uint8_t* vars32, uint64_t n_vars, const uint8_t* inputs32,
+                     uint64_t n_inputs, const sb200_gens* gens, const sb200_transcript_vt* transcript,
+                     const uint8_t* label, size_t label_len, const uint8_t* tape_seed64, const sb200_comm_vt* comm,
+                     uint8_t** proof_out, size_t* proof_len);
+
+/* NIZK::verify(&self, &inst, &inputs, &mut transcript, &gens)            lib.rs:538-574
+ * 0 = accepted; SB200_ERR_PROOF_VERIFY where the reference returns Err or panics;
+ * SB200_ERR_PROOF_MALFORMED if the bytes do not parse as bincode(NIZK). */
+int sb200_nizk_verify(const sb200_instance* inst, const uint8_t* inputs32, uint64_t n_inputs, const sb200_gens* gens,
+                      const sb200_transcript_vt* transcript, const uint8_t* label, size_t label_len,
+                      const uint8_t* proof, size_t proof_len);
+
+/* Timer scopes of the last prove on this thread, seconds               timer.rs, r1csproof.rs:155-307
+ * out[0..7] = polycommit, prove_sc_phase_one, prove_sc_phase_two, polyeval,
+ *             total, h2d (inside total), host Fiat-Shamir time (inside total), kernel launches */
+int sb200_last_prove_profile(double out[8]);
+
+void sb200_free(void* p);
+const char* sb200_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPARTAN_B200_H */

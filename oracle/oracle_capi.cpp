@@ -49,6 +49,11 @@ int orc_pt_add(const uint8_t a[32], const uint8_t b[32], uint8_t out[32]) {
   Pt p, q; if (!pt_decompress(a, p) || !pt_decompress(b, q)) return 0;
   pt_compress(pt_add(p, q), out); return 1;
 }
+// affine (x, y) canonical LE of a compressed point (the ristretto representative decompress() yields)
+int orc_pt_affine(const uint8_t a[32], uint8_t out[64]) {
+  Pt p; if (!pt_decompress(a, p)) return 0;
+  fp_to_bytes(p.X, out); fp_to_bytes(p.Y, out + 32); return 1;
+}
 int orc_pt_decompress_ok(const uint8_t a[32]) { Pt p; return pt_decompress(a, p); }
 void orc_from_uniform_bytes(const uint8_t in[64], uint8_t out[32]) { pt_compress(pt_from_uniform_bytes(in), out); }
 // sum_i k_i * P_i (k Montgomery limbs, P compressed)

@@ -1,0 +1,94 @@
+// Host-callable launchers of the sm_100a kernels (kernels.cu).  Pointers are
+// device pointers unless the name says host.  Everything runs on the stream
+// passed in; nothing here synchronises unless stated.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "fl.cuh"
+
+namespace sb {
+
+struct niels_t;
+
+// ---- fixed-base tables (one per NIZKGens) -------------------------------------------------
+struct MsmTable {
+  niels_t* tbl = nullptr;  // [nbases][windows][1 << (c-1)] affine Niels entries
+  uint32_t nbases = 0;     // R + 2 : G[0..R-1], h, Q (= gens_1.G[0])
+  uint32_t c = 0;          // window bits
+  uint32_t windows = 0;    // floor(252/c) + 1
+  size_t entries_per_base() const { return (size_t)windows << (c - 1); }
+};
+// affine_xy: host array, nbases x 64 bytes (x, y canonical LE).  Allocates and fills t.tbl.
+cudaError_t msm_table_build(MsmTable& t, const uint8_t* affine_xy_host, uint32_t nbases, uint32_t c, cudaStream_t s);
+void msm_table_free(MsmTable& t);
+
+// rows x n fixed-base MSM over bases [0, n) plus optional per-row scalars for base n_h (h) and
+// n_q (Q).  scalars: canonical integers < l, row-major with row stride `stride` (in scalars).
+// out32: rows x 32-byte compressed ristretto points.  `scratch` must hold rows*splits*128 bytes.
+struct MsmPlan {
+  uint32_t rows, n, splits;
+};
+MsmPlan msm_plan(uint32_t rows, uint32_t n);
+cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n,
+                      const fl_t* extra_h, const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch,
+                      uint8_t* out32, cudaStream_t s);
+size_t msm_scratch_bytes(uint32_t rows, uint32_t n);
+
+// ---- F_l vector kernels -------------------------------------------------------------------
+// canonical -> Montgomery, flag[0] |= 1 if any input >= l            (lib.rs:65-89)
+cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s);
+cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s);
+// out[i] = a[i] op b[i]  (op 0 add, 1 sub, 2 mul) -- parity-test hook for the limb arithmetic
+cudaError_t k_fl_binop(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n, cudaStream_t s);
+// flag[0] |= 1 unless A[i]*B[i] == C[i] for all i                     (r1csinstance.rs:238-245)
+cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, uint32_t* flag, cudaStream_t s);
+// eq(r) table of length 2^ell                                         (dense_mlpoly.rs:67-83)
+// r: device array of ell Montgomery scalars; tmp: >= 2^ceil(ell/2)+2^floor(ell/2) scalars
+cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s);
+
+struct Csr {  // three matrices share the layout
+  const uint32_t* ptr[3];
+  const uint32_t* idx[3];
+  const fl_t* val[3];
+};
+// y[m][row] = sum val * z[col]                                        (sparse_mlpoly.rs:452-466)
+cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s);
+// out[col] = rA*sum_A e[row]*val + rB*... + rC*...                    (sparse_mlpoly.rs:468-483, r1csproof.rs:268-279)
+cudaError_t k_spmvT3_combine(const Csr& csc, uint32_t num_cols, const fl_t* e, fl_t rA, fl_t rB, fl_t rC, fl_t* out,
+                             cudaStream_t s);
+
+// Sum-check workspace for the cross-block reduction
+struct ScWork {
+  fl_t* partials;      // [max_blocks][3]
+  unsigned int* counter;
+  fl_t* result;        // device [3]
+  uint32_t max_blocks;
+};
+// One fused round of the cubic ZK sum-check (sumcheck.rs:618-674):
+//  if do_bind: tables (length n_old) are bound at r in place -> length n_old/2   (dense_mlpoly.rs:214-221)
+//  then e0,e2,e3 of the (new) tables are reduced into w.result.
+cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind, fl_t r, const ScWork& w,
+                       cudaStream_t s);
+// Same for the quadratic sum-check (sumcheck.rs:453-484): result = e0, e2, (0)
+cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s);
+
+// LZ[i] = sum_j Lv[j] * Z[j*R + i]                                    (dense_mlpoly.rs:205-212)
+cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rsize, fl_t* out, fl_t* tmp,
+                      cudaStream_t s);
+size_t bound_L_tmp_scalars(uint32_t Lsize, uint32_t Rsize);
+// out[0] = <a, b>   (n <= 2^16, one block)                            (nizk/mod.rs:305-308)
+cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cudaStream_t s);
+
+// Bullet reduction scalar side (nizk/bullet.rs:71-118), see kernels.cu
+cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize,
+                          bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR,
+                          cudaStream_t s);
+// s[g] = from_mont(d * coeff[g]) for g < R                            (nizk/mod.rs:483-490)
+cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s);
+
+// counter of kernel launches issued through this file (bench.py gpu_launches)
+uint64_t launch_count();
+void launch_count_reset();
+
+}  // namespace sb

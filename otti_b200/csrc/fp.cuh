@@ -1,0 +1,216 @@
+// F_p device arithmetic, p = 2^255 - 19, for Edwards25519 / ristretto255
+// coordinates (the reference gets these from curve25519-dalek 3.2; call sites
+// Spartan/src/group.rs:6-7,98-117, commitments.rs:79-84).
+//
+// Representation: 8 x u32 little-endian limbs holding ANY value in [0, 2^256)
+// congruent to the element ("loose" form).  2^256 = 38 (mod p), so carries out
+// of bit 256 fold back in as +38 and never need a compare.  fp_canon() gives
+// the unique representative in [0, p) for compress / equality / sign.
+// Plain C, __host__ __device__: the limb logic is unit-tested on the CPU.
+#pragma once
+#include "fl.cuh"
+
+namespace sb {
+
+struct alignas(16) fp_t {
+  uint32_t v[8];
+};
+
+SB_HD fp_t fp_zero() {
+  fp_t r;
+#pragma unroll
+  for (int i = 0; i < 8; i++) r.v[i] = 0;
+  return r;
+}
+SB_HD fp_t fp_one() {
+  fp_t r = fp_zero();
+  r.v[0] = 1;
+  return r;
+}
+SB_HD fp_t fp_set(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t a4, uint32_t a5, uint32_t a6, uint32_t a7) {
+  fp_t r;
+  r.v[0] = a0; r.v[1] = a1; r.v[2] = a2; r.v[3] = a3; r.v[4] = a4; r.v[5] = a5; r.v[6] = a6; r.v[7] = a7;
+  return r;
+}
+// 2d mod p, d = -121665/121666
+SB_HD fp_t fp_2d() { return fp_set(0x26b2f159u, 0xebd69b94u, 0x8283b156u, 0x00e0149au, 0xeef3d130u, 0x198e80f2u, 0x56dffce7u, 0x2406d9dcu); }
+SB_HD fp_t fp_d() { return fp_set(0x135978a3u, 0x75eb4dcau, 0x4141d8abu, 0x00700a4du, 0x7779e898u, 0x8cc74079u, 0x2b6ffe73u, 0x52036ceeu); }
+
+// r = x + 38*k (k in {0,1,2...small}), folding the (at most one) further carry
+SB_HD fp_t fp_fold_small(const fp_t& x, uint32_t k38) {
+  fp_t r;
+  uint64_t c = k38;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += x.v[i];
+    r.v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  // a second wrap can only happen when the low limbs are tiny, so +38 cannot carry past limb 0's neighbours
+  uint32_t k2 = (uint32_t)c * 38u;
+  c = k2;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += r.v[i];
+    r.v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  return r;
+}
+SB_HD fp_t fp_add(const fp_t& a, const fp_t& b) {
+  fp_t t;
+  uint64_t c = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += (uint64_t)a.v[i] + b.v[i];
+    t.v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  return fp_fold_small(t, (uint32_t)c * 38u);
+}
+SB_HD fp_t fp_sub(const fp_t& a, const fp_t& b) {
+  fp_t d;
+  uint64_t borrow = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    uint64_t x = (uint64_t)a.v[i] - b.v[i] - borrow;
+    d.v[i] = (uint32_t)x;
+    borrow = x >> 63;
+  }
+  // a - b + 2^256 == a - b + 38 (mod p): subtract 38 when we wrapped
+  uint64_t k = borrow * 38u;
+  borrow = 0;
+  fp_t r;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    uint64_t x = (uint64_t)d.v[i] - (i == 0 ? k : 0) - borrow;
+    r.v[i] = (uint32_t)x;
+    borrow = x >> 63;
+  }
+  k = borrow * 38u;  // wrapped again (d was < 38): one more -38 cannot wrap a third time
+  borrow = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    uint64_t x = (uint64_t)r.v[i] - (i == 0 ? k : 0) - borrow;
+    r.v[i] = (uint32_t)x;
+    borrow = x >> 63;
+  }
+  return r;
+}
+SB_HD fp_t fp_neg(const fp_t& a) { return fp_sub(fp_zero(), a); }
+
+// 16-limb product folded to 8 limbs: lo + 38*hi
+SB_HD fp_t fp_reduce16(const uint32_t t[16]) {
+  uint32_t r[9];
+  uint64_t c = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += (uint64_t)t[i + 8] * 38u + t[i];
+    r[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  fp_t x;
+#pragma unroll
+  for (int i = 0; i < 8; i++) x.v[i] = r[i];
+  return fp_fold_small(x, (uint32_t)c * 38u);  // c < 39 -> c*38 < 2^11
+}
+SB_HD fp_t fp_mul(const fp_t& a, const fp_t& b) {
+  uint32_t t[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) t[i] = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    uint64_t c = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      c += (uint64_t)a.v[j] * b.v[i] + t[i + j];
+      t[i + j] = (uint32_t)c;
+      c >>= 32;
+    }
+    t[i + 8] = (uint32_t)c;
+  }
+  return fp_reduce16(t);
+}
+SB_HD fp_t fp_sqr(const fp_t& a) { return fp_mul(a, a); }
+SB_HD fp_t fp_mul_small(const fp_t& a, uint32_t k) {  // k < 2^26
+  fp_t x;
+  uint64_t c = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += (uint64_t)a.v[i] * k;
+    x.v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  return fp_fold_small(x, (uint32_t)c * 38u);
+}
+
+// unique representative in [0, p)
+SB_HD fp_t fp_canon(const fp_t& a) {
+  // fold bit 255: x = (a mod 2^255) + 19*(a >> 255)   -> x < 2^255 + 19
+  fp_t x = a;
+  uint32_t top = x.v[7] >> 31;
+  x.v[7] &= 0x7fffffffu;
+  uint64_t c = top * 19u;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    c += x.v[i];
+    x.v[i] = (uint32_t)c;
+    c >>= 32;
+  }
+  // now x < 2^255 + 19 <= 2p + ...; subtract p while x >= p (at most twice)
+#pragma unroll
+  for (int rep = 0; rep < 2; rep++) {
+    // x >= p  <=>  x + 19 >= 2^255
+    uint64_t cc = 19;
+    uint32_t y[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      cc += x.v[i];
+      y[i] = (uint32_t)cc;
+      cc >>= 32;
+    }
+    uint32_t ge = (y[7] >> 31) | (uint32_t)cc;  // bit 255 (or beyond) set
+    y[7] &= 0x7fffffffu;                        // x + 19 - 2^255 = x - p
+    if (ge) {
+#pragma unroll
+      for (int i = 0; i < 8; i++) x.v[i] = y[i];
+    }
+  }
+  return x;
+}
+SB_HD bool fp_is_zero(const fp_t& a) {
+  fp_t c = fp_canon(a);
+  uint32_t o = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) o |= c.v[i];
+  return o == 0;
+}
+SB_HD bool fp_eq(const fp_t& a, const fp_t& b) { return fp_is_zero(fp_sub(a, b)); }
+SB_HD bool fp_is_neg(const fp_t& a) { return fp_canon(a).v[0] & 1u; }
+SB_HD fp_t fp_abs(const fp_t& a) { return fp_is_neg(a) ? fp_neg(a) : a; }
+
+SB_HD fp_t fp_pow2k(fp_t a, int k) {
+  for (int i = 0; i < k; i++) a = fp_sqr(a);
+  return a;
+}
+// a^((p-5)/8) = a^(2^252 - 3)
+SB_HD fp_t fp_pow_p58(const fp_t& z) {
+  fp_t z2 = fp_sqr(z), z9 = fp_mul(fp_pow2k(z2, 2), z), z11 = fp_mul(z9, z2);
+  fp_t z2_5_0 = fp_mul(fp_sqr(z11), z9);
+  fp_t z2_10_0 = fp_mul(fp_pow2k(z2_5_0, 5), z2_5_0);
+  fp_t z2_20_0 = fp_mul(fp_pow2k(z2_10_0, 10), z2_10_0);
+  fp_t z2_40_0 = fp_mul(fp_pow2k(z2_20_0, 20), z2_20_0);
+  fp_t z2_50_0 = fp_mul(fp_pow2k(z2_40_0, 10), z2_10_0);
+  fp_t z2_100_0 = fp_mul(fp_pow2k(z2_50_0, 50), z2_50_0);
+  fp_t z2_200_0 = fp_mul(fp_pow2k(z2_100_0, 100), z2_100_0);
+  fp_t z2_250_0 = fp_mul(fp_pow2k(z2_200_0, 50), z2_50_0);
+  return fp_mul(fp_pow2k(z2_250_0, 2), z);
+}
+// a^(p-2)
+SB_HD fp_t fp_invert(const fp_t& z) {
+  // a^(2^255-21) = (a^(2^252-3))^8 * a^3
+  fp_t t = fp_pow2k(fp_pow_p58(z), 3);
+  return fp_mul(t, fp_mul(fp_sqr(z), z));
+}
+
+}  // namespace sb

@@ -1,0 +1,98 @@
+// Host-side objects behind the opaque C-ABI handles: the R1CS instance (device
+// CSR + CSC of A, B, C), the NIZK generators (host fixed-base tables for the
+// Fiat-Shamir tail + device window tables for the commitment kernel) and the
+// per-instance device workspace.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../dev.hpp"
+#include "hge.hpp"
+#include "hmerlin.hpp"
+
+namespace sbh {
+
+// thread-local error text for sb200_last_error()
+void set_error(const std::string& s);
+const char* get_error();
+
+#define SB_CUDA(expr)                                                                   \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      sbh::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));               \
+      return SB200_ERR_CUDA;                                                            \
+    }                                                                                   \
+  } while (0)
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  cudaError_t alloc(size_t count) {
+    release();
+    n = count;
+    if (!count) return cudaSuccess;
+    return cudaMalloc((void**)&p, count * sizeof(T));
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+};
+
+struct SparseDev {  // CSR (by row) or CSC (by column) of the three matrices
+  DevBuf<uint32_t> ptr[3], idx[3];
+  DevBuf<sb::fl_t> val[3];
+  sb::Csr view() const {
+    sb::Csr c;
+    for (int m = 0; m < 3; m++) { c.ptr[m] = ptr[m].p; c.idx[m] = idx[m].p; c.val[m] = val[m].p; }
+    return c;
+  }
+};
+
+struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
+  bool ready = false;
+  DevBuf<sb::fl_t> vars_canon, varsM, z, abc, T, A, B, C, eq_tmp, sc_partials, small, blinds, bound_tmp, LZ, bl_a, bl_b,
+      coeff0, coeff1, srows;
+  DevBuf<unsigned int> counter;
+  DevBuf<uint32_t> flag;
+  DevBuf<uint8_t> msm_scratch, pts;
+  uint8_t* pinned = nullptr;  // host staging
+  size_t pinned_bytes = 0;
+  cudaStream_t stream = nullptr;
+  ~Workspace() {
+    if (pinned) cudaFreeHost(pinned);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+struct Instance {
+  uint64_t num_cons = 0, num_vars = 0, num_inputs = 0;  // padded, lib.rs:130-158
+  uint64_t nnz[3] = {0, 0, 0};
+  SparseDev csr, csc;
+  mutable Workspace ws;
+};
+
+struct Gens {
+  uint64_t num_vars_padded = 0;
+  uint32_t R = 0;  // gens_n.n = 2^(ell - ell/2)
+  // host points: G[0..R-1], h, Q = gens_1.G[0]; sum-check generators G4[0..3], h4 (h3 == G4[3])
+  std::vector<Ge> G;
+  Ge h, Q, G4[4], h4;
+  // fixed-base tables for the 7 generators of the Fiat-Shamir tail
+  FixedBase fb_G4[4], fb_h4, fb_Q, fb_h;
+  sb::MsmTable table;  // device: bases [0,R) = G, R = h, R+1 = Q
+  ~Gens() { sb::msm_table_free(table); }
+};
+
+}  // namespace sbh

@@ -1,0 +1,654 @@
+// sm_100a kernels for the Spartan NIZK prover hot loops.
+// All arithmetic is exact 253/255-bit modular integer work on the IMAD pipe -- no
+// tensor cores by design.  Kernel <-> reference map:
+//   k_to_mont          Assignment::new / Scalar::from_bytes        lib.rs:65-89
+//   k_eq_table         EqPolynomial::evals                         dense_mlpoly.rs:67-83
+//   k_spmv3            R1CSInstance::multiply_vec                  r1csinstance.rs:248-262, sparse_mlpoly.rs:452-466
+//   k_sc_cubic         prove_cubic_with_additive_term round + 4x bound_poly_var_top
+//                                                                  sumcheck.rs:618-674, dense_mlpoly.rs:214-221
+//   k_spmvT3_combine   compute_eval_table_sparse x3 + r_A/r_B/r_C  sparse_mlpoly.rs:468-483, r1csproof.rs:268-279
+//   k_sc_quad          prove_quad round + 2x bound_poly_var_top    sumcheck.rs:453-484
+//   k_bound_L          DensePolynomial::bound                      dense_mlpoly.rs:205-212
+//   k_dot_small        DotProductProofLog::compute_dotproduct      nizk/mod.rs:430-433
+//   k_bullet_step      BulletReductionProof::prove scalar side     nizk/bullet.rs:71-118
+//   msm_fixed          [Scalar]::commit -> vartime_multiscalar_mul commitments.rs:79-84, dense_mlpoly.rs:163-176
+#include <atomic>
+#include <cstdio>
+
+#include "dev.hpp"
+#include "ge.cuh"
+
+namespace sb {
+
+static std::atomic<uint64_t> g_launches{0};
+uint64_t launch_count() { return g_launches.load(); }
+void launch_count_reset() { g_launches.store(0); }
+#define SB_LAUNCHED() (g_launches.fetch_add(1), cudaGetLastError())
+
+static constexpr int kSMs = 148;  // B200
+
+// ------------------------------------------------------------------ 128-bit memory helpers
+__device__ __forceinline__ fl_t ld_fl(const fl_t* p) {
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 a = q[0], b = q[1];
+  fl_t r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ fl_t ldg_fl(const fl_t* p) {  // read-only path
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 a = __ldg(q), b = __ldg(q + 1);
+  fl_t r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ fl_t ldcg_fl(const fl_t* p) {  // L2 only (cross-block visibility)
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 a = __ldcg(q), b = __ldcg(q + 1);
+  fl_t r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ void st_fl(fl_t* p, const fl_t& x) {
+  uint4* q = reinterpret_cast<uint4*>(p);
+  q[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]);
+  q[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+}
+__device__ __forceinline__ fp_t ldg_fp(const fp_t* p) {
+  const uint4* q = reinterpret_cast<const uint4*>(p);
+  uint4 a = __ldg(q), b = __ldg(q + 1);
+  fp_t r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+__device__ __forceinline__ void st_fp(fp_t* p, const fp_t& x) {
+  uint4* q = reinterpret_cast<uint4*>(p);
+  q[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]);
+  q[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+}
+
+// ------------------------------------------------------------------ reductions over F_l
+__device__ __forceinline__ fl_t warp_sum_fl(fl_t x) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    fl_t y;
+#pragma unroll
+    for (int i = 0; i < 8; i++) y.v[i] = __shfl_down_sync(0xffffffffu, x.v[i], o);
+    x = fl_add(x, y);
+  }
+  return x;
+}
+// Sum NV values per thread over the block; valid in thread 0.  smem: fl_t[NV * 32].
+template <int NV>
+__device__ __forceinline__ void block_sum_fl(fl_t (&x)[NV], fl_t* smem) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; k++) x[k] = warp_sum_fl(x[k]);
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) smem[wid * NV + k] = x[k];
+  }
+  __syncthreads();
+  if (wid == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      fl_t v = lane < nw ? smem[lane * NV + k] : fl_zero();
+      x[k] = warp_sum_fl(v);
+    }
+  }
+}
+// Grid-wide sum by "last block done": every block deposits NV partials, the last one to
+// arrive adds them up (F_l addition is exact, so arrival order cannot change a bit).
+template <int NV>
+__device__ __forceinline__ void grid_sum_fl(fl_t (&x)[NV], fl_t* smem, fl_t* partials, unsigned int* counter, fl_t* result) {
+  __shared__ bool s_last;
+  block_sum_fl<NV>(x, smem);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) st_fl(&partials[(size_t)blockIdx.x * NV + k], x[k]);
+    __threadfence();
+    unsigned int t = atomicAdd(counter, 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last) {
+    fl_t acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; k++) acc[k] = fl_zero();
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+#pragma unroll
+      for (int k = 0; k < NV; k++) acc[k] = fl_add(acc[k], ldcg_fl(&partials[(size_t)b * NV + k]));
+    }
+    block_sum_fl<NV>(acc, smem);
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; k++) st_fl(&result[k], acc[k]);
+      *counter = 0;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ elementwise
+__global__ void to_mont_kernel(const fl_t* __restrict__ in, fl_t* __restrict__ out, size_t n, uint32_t* flag) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  bool bad = false;
+  for (; i < n; i += stride) {
+    fl_t x = ldg_fl(in + i);
+    bad |= !fl_is_canonical(x);
+    st_fl(out + i, fl_to_mont(x));
+  }
+  if (bad) atomicOr(flag, 1u);
+}
+__global__ void from_mont_kernel(const fl_t* __restrict__ in, fl_t* __restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) st_fl(out + i, fl_from_mont(ldg_fl(in + i)));
+}
+__global__ void fl_binop_kernel(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    fl_t x = ld_fl(a + i), y = ld_fl(b + i);
+    st_fl(out + i, op == 0 ? fl_add(x, y) : op == 1 ? fl_sub(x, y) : fl_mul(x, y));
+  }
+}
+static inline unsigned grid_for(size_t n, int block, int per_sm = 8) {
+  size_t g = (n + block - 1) / block;
+  size_t cap = (size_t)kSMs * per_sm;
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n, flag);
+  return SB_LAUNCHED();
+}
+cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  from_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n);
+  return SB_LAUNCHED();
+}
+cudaError_t k_fl_binop(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  fl_binop_kernel<<<grid_for(n, 256), 256, 0, s>>>(op, a, b, out, n);
+  return SB_LAUNCHED();
+}
+
+// flag |= 1 if Az[i]*Bz[i] != Cz[i] for some i        (r1csinstance.rs:238-245)
+__global__ void check_sat_kernel(const fl_t* __restrict__ A, const fl_t* __restrict__ B, const fl_t* __restrict__ C, size_t n,
+                                 uint32_t* flag) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  bool bad = false;
+  for (; i < n; i += stride) bad |= !fl_eq(fl_mul(ld_fl(A + i), ld_fl(B + i)), ld_fl(C + i));
+  if (bad) atomicOr(flag, 1u);
+}
+cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, uint32_t* flag, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  check_sat_kernel<<<grid_for(n, 256), 256, 0, s>>>(A, B, C, n, flag);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ eq table
+// E[i] = prod_j (bit_{ell-1-j}(i) ? r[j] : 1 - r[j])  -- thread per entry, used for the two
+// half-size factor tables (<= 2^12 entries each).
+__global__ void eq_small_kernel(const fl_t* __restrict__ r, uint32_t ell, fl_t* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (1u << ell)) return;
+  fl_t acc = fl_one(), one = fl_one();
+  for (uint32_t j = 0; j < ell; j++) {
+    fl_t rj = ldg_fl(r + j);
+    bool bit = (i >> (ell - 1 - j)) & 1u;
+    acc = fl_mul(acc, bit ? rj : fl_sub(one, rj));
+  }
+  st_fl(out + i, acc);
+}
+// out[(ih << b) | il] = hi[ih] * lo[il]: one multiplication and one 32-byte store per entry.
+__global__ void eq_outer_kernel(const fl_t* __restrict__ hi, const fl_t* __restrict__ lo, uint32_t b, size_t n,
+                                fl_t* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  const size_t mask = ((size_t)1 << b) - 1;
+  for (; i < n; i += stride) st_fl(out + i, fl_mul(ldg_fl(hi + (i >> b)), ldg_fl(lo + (i & mask))));
+}
+cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s) {
+  if (ell <= 8) {
+    eq_small_kernel<<<((1u << ell) + 127) / 128, 128, 0, s>>>(r, ell, out);
+    return SB_LAUNCHED();
+  }
+  uint32_t a = ell / 2, b = ell - a;  // high a variables (r[0..a)), low b variables
+  fl_t* hi = tmp;
+  fl_t* lo = tmp + ((size_t)1 << a);
+  eq_small_kernel<<<((1u << a) + 127) / 128, 128, 0, s>>>(r, a, hi);
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  eq_small_kernel<<<((1u << b) + 127) / 128, 128, 0, s>>>(r + a, b, lo);
+  e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  size_t n = (size_t)1 << ell;
+  eq_outer_kernel<<<grid_for(n, 256), 256, 0, s>>>(hi, lo, b, n, out);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ sparse mat-vec
+__global__ void spmv3_kernel(Csr csr, uint32_t num_rows, const fl_t* __restrict__ z, fl_t* __restrict__ yA,
+                             fl_t* __restrict__ yB, fl_t* __restrict__ yC) {
+  const int m = blockIdx.y;
+  const uint32_t* __restrict__ ptr = csr.ptr[m];
+  const uint32_t* __restrict__ idx = csr.idx[m];
+  const fl_t* __restrict__ val = csr.val[m];
+  fl_t* y = m == 0 ? yA : m == 1 ? yB : yC;
+  for (uint32_t row = blockIdx.x * blockDim.x + threadIdx.x; row < num_rows; row += gridDim.x * blockDim.x) {
+    uint32_t k0 = __ldg(ptr + row), k1 = __ldg(ptr + row + 1);
+    fl_t acc = fl_zero();
+    for (uint32_t k = k0; k < k1; k++) acc = fl_add(acc, fl_mul(ldg_fl(val + k), ldg_fl(z + __ldg(idx + k))));
+    st_fl(y + row, acc);
+  }
+}
+cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s) {
+  dim3 grid(grid_for(num_rows, 128), 3);
+  spmv3_kernel<<<grid, 128, 0, s>>>(csr, num_rows, z, yA, yB, yC);
+  return SB_LAUNCHED();
+}
+__global__ void spmvT3_kernel(Csr csc, uint32_t num_cols, const fl_t* __restrict__ e, fl_t rA, fl_t rB, fl_t rC,
+                              fl_t* __restrict__ out) {
+  for (uint32_t col = blockIdx.x * blockDim.x + threadIdx.x; col < num_cols; col += gridDim.x * blockDim.x) {
+    fl_t tot = fl_zero();
+#pragma unroll
+    for (int m = 0; m < 3; m++) {
+      uint32_t k0 = __ldg(csc.ptr[m] + col), k1 = __ldg(csc.ptr[m] + col + 1);
+      if (k0 == k1) continue;
+      fl_t acc = fl_zero();
+      for (uint32_t k = k0; k < k1; k++)
+        acc = fl_add(acc, fl_mul(ldg_fl(e + __ldg(csc.idx[m] + k)), ldg_fl(csc.val[m] + k)));
+      tot = fl_add(tot, fl_mul(m == 0 ? rA : m == 1 ? rB : rC, acc));
+    }
+    st_fl(out + col, tot);
+  }
+}
+cudaError_t k_spmvT3_combine(const Csr& csc, uint32_t num_cols, const fl_t* e, fl_t rA, fl_t rB, fl_t rC, fl_t* out,
+                             cudaStream_t s) {
+  spmvT3_kernel<<<grid_for(num_cols, 128), 128, 0, s>>>(csc, num_cols, e, rA, rB, rC, out);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ sum-check rounds
+__device__ __forceinline__ fl_t bind1(const fl_t& lo, const fl_t& hi, const fl_t& r) {
+  return fl_add(lo, fl_mul(r, fl_sub(hi, lo)));  // Z[i] + r*(Z[i+n] - Z[i]), dense_mlpoly.rs:217
+}
+template <bool BIND>
+__global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
+                                                       fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
+                                                       unsigned int* counter, fl_t* result) {
+  __shared__ fl_t smem[3 * 32];
+  const size_t h = newlen >> 1;
+  fl_t e[3];
+  e[0] = e[1] = e[2] = fl_zero();
+  fl_t* tabs[4] = {T, A, B, C};
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < h; i += (size_t)gridDim.x * blockDim.x) {
+    fl_t lo[4], hi[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      fl_t* X = tabs[k];
+      if (BIND) {
+        lo[k] = bind1(ld_fl(X + i), ld_fl(X + i + newlen), r);
+        hi[k] = bind1(ld_fl(X + i + h), ld_fl(X + i + h + newlen), r);
+        st_fl(X + i, lo[k]);
+        st_fl(X + i + h, hi[k]);
+      } else {
+        lo[k] = ld_fl(X + i);
+        hi[k] = ld_fl(X + i + h);
+      }
+    }
+    // comb(T,A,B,C) = T*(A*B - C) at the points 0, 2, 3 (sumcheck.rs:622-650, r1csproof.rs:84-88)
+    e[0] = fl_add(e[0], fl_mul(lo[0], fl_sub(fl_mul(lo[1], lo[2]), lo[3])));
+    fl_t d[4], p[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      d[k] = fl_sub(hi[k], lo[k]);
+      p[k] = fl_add(hi[k], d[k]);  // 2*hi - lo
+    }
+    e[1] = fl_add(e[1], fl_mul(p[0], fl_sub(fl_mul(p[1], p[2]), p[3])));
+#pragma unroll
+    for (int k = 0; k < 4; k++) p[k] = fl_add(p[k], d[k]);  // 3*hi - 2*lo
+    e[2] = fl_add(e[2], fl_mul(p[0], fl_sub(fl_mul(p[1], p[2]), p[3])));
+  }
+  if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) st_fl(tabs[k], bind1(ld_fl(tabs[k]), ld_fl(tabs[k] + 1), r));
+  }
+  grid_sum_fl<3>(e, smem, partials, counter, result);
+}
+template <bool BIND>
+__global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
+                                                      fl_t* partials, unsigned int* counter, fl_t* result) {
+  __shared__ fl_t smem[3 * 32];
+  const size_t h = newlen >> 1;
+  fl_t e[3];
+  e[0] = e[1] = e[2] = fl_zero();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < h; i += (size_t)gridDim.x * blockDim.x) {
+    fl_t zl, zh, ql, qh;
+    if (BIND) {
+      zl = bind1(ld_fl(Z + i), ld_fl(Z + i + newlen), r);
+      zh = bind1(ld_fl(Z + i + h), ld_fl(Z + i + h + newlen), r);
+      ql = bind1(ld_fl(Q + i), ld_fl(Q + i + newlen), r);
+      qh = bind1(ld_fl(Q + i + h), ld_fl(Q + i + h + newlen), r);
+      st_fl(Z + i, zl); st_fl(Z + i + h, zh); st_fl(Q + i, ql); st_fl(Q + i + h, qh);
+    } else {
+      zl = ld_fl(Z + i); zh = ld_fl(Z + i + h); ql = ld_fl(Q + i); qh = ld_fl(Q + i + h);
+    }
+    e[0] = fl_add(e[0], fl_mul(zl, ql));  // sumcheck.rs:459-467
+    fl_t z2 = fl_sub(fl_add(zh, zh), zl), q2 = fl_sub(fl_add(qh, qh), ql);
+    e[1] = fl_add(e[1], fl_mul(z2, q2));
+  }
+  if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
+    st_fl(Z, bind1(ld_fl(Z), ld_fl(Z + 1), r));
+    st_fl(Q, bind1(ld_fl(Q), ld_fl(Q + 1), r));
+  }
+  grid_sum_fl<3>(e, smem, partials, counter, result);
+}
+static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
+  size_t g = (pairs + 255) / 256;
+  size_t cap = (size_t)kSMs * 4;
+  if (cap > w.max_blocks) cap = w.max_blocks;
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind, fl_t r, const ScWork& w,
+                       cudaStream_t s) {
+  size_t newlen = do_bind ? n_old / 2 : n_old;
+  unsigned g = sc_grid(newlen / 2, w);
+  if (do_bind) sc_cubic_kernel<true><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result);
+  else sc_cubic_kernel<false><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result);
+  return SB_LAUNCHED();
+}
+cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s) {
+  size_t newlen = do_bind ? n_old / 2 : n_old;
+  unsigned g = sc_grid(newlen / 2, w);
+  if (do_bind) sc_quad_kernel<true><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result);
+  else sc_quad_kernel<false><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ bound(L), dot
+// grid (ceil(R/128), JC): tmp[jc*R + i] = sum_{j in chunk jc} Lv[j] * Z[j*R + i]
+__global__ void bound_partial_kernel(const fl_t* __restrict__ Z, const fl_t* __restrict__ Lv, uint32_t Lsize,
+                                     uint32_t Rsize, uint32_t jper, fl_t* __restrict__ tmp) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Rsize) return;
+  uint32_t j0 = blockIdx.y * jper, j1 = min(Lsize, j0 + jper);
+  fl_t acc = fl_zero();
+  for (uint32_t j = j0; j < j1; j++) acc = fl_add(acc, fl_mul(ldg_fl(Lv + j), ldg_fl(Z + (size_t)j * Rsize + i)));
+  st_fl(tmp + (size_t)blockIdx.y * Rsize + i, acc);
+}
+__global__ void bound_sum_kernel(const fl_t* __restrict__ tmp, uint32_t Rsize, uint32_t jc, fl_t* __restrict__ out) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Rsize) return;
+  fl_t acc = fl_zero();
+  for (uint32_t c = 0; c < jc; c++) acc = fl_add(acc, ld_fl(tmp + (size_t)c * Rsize + i));
+  st_fl(out + i, acc);
+}
+static inline uint32_t bound_chunks(uint32_t Lsize, uint32_t Rsize) {
+  uint32_t want = (uint32_t)((size_t)kSMs * 1024 / (Rsize ? Rsize : 1));
+  if (want < 1) want = 1;
+  if (want > Lsize) want = Lsize;
+  return want;
+}
+size_t bound_L_tmp_scalars(uint32_t Lsize, uint32_t Rsize) { return (size_t)bound_chunks(Lsize, Rsize) * Rsize; }
+cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rsize, fl_t* out, fl_t* tmp, cudaStream_t s) {
+  uint32_t jc = bound_chunks(Lsize, Rsize), jper = (Lsize + jc - 1) / jc;
+  jc = (Lsize + jper - 1) / jper;
+  dim3 grid((Rsize + 127) / 128, jc);
+  bound_partial_kernel<<<grid, 128, 0, s>>>(Z, Lv, Lsize, Rsize, jper, tmp);
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  bound_sum_kernel<<<(Rsize + 127) / 128, 128, 0, s>>>(tmp, Rsize, jc, out);
+  return SB_LAUNCHED();
+}
+__global__ void dot_small_kernel(const fl_t* __restrict__ a, const fl_t* __restrict__ b, uint32_t n, fl_t* out) {
+  __shared__ fl_t smem[32];
+  fl_t acc[1];
+  acc[0] = fl_zero();
+  for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) acc[0] = fl_add(acc[0], fl_mul(ld_fl(a + i), ld_fl(b + i)));
+  block_sum_fl<1>(acc, smem);
+  if (threadIdx.x == 0) st_fl(out, acc[0]);
+}
+cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cudaStream_t s) {
+  dot_small_kernel<<<1, 1024, 0, s>>>(a, b, n, out);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ bullet reduction, scalar side
+// One block.  State: a, b (length n_cur, Montgomery), coeff (length R/n_cur) with
+//   G_k[i] = sum_t coeff[t] * G[t*n_cur + i]           (the folded generators, never materialised)
+// Step:  (1) if do_fold: a_L*u + u^-1*a_R, b_L*u^-1 + u*b_R, coeff' = coeff (x) (u^-1, u)   bullet.rs:103-108
+//        (2) if n > 1: c_L = <a_L,b_R>, c_R = <a_R,b_L> and the two MSM scalar rows over the ORIGINAL
+//            bases:  L = sum a_L[i]*G_R[i] + c_L*Q + blind_L*H,  R = sum a_R[i]*G_L[i] + c_R*Q + blind_R*H
+//            (bullet.rs:79-96).  Rows have stride R+2: [0,R) bases G, [R] = H, [R+1] = Q; canonical form.
+__global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, const fl_t* coeff_in, fl_t* coeff_out,
+                                                           uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv,
+                                                           fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR) {
+  __shared__ fl_t smem[2 * 32];
+  uint32_t n = n_cur;
+  const uint32_t nco_in = Rsize / n_cur;
+  if (do_fold) {
+    n = n_cur / 2;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+      fl_t al = ld_fl(a + i), ar = ld_fl(a + n + i), bl = ld_fl(b + i), br = ld_fl(b + n + i);
+      st_fl(a + i, fl_add(fl_mul(al, u), fl_mul(u_inv, ar)));
+      st_fl(b + i, fl_add(fl_mul(bl, u_inv), fl_mul(u, br)));
+    }
+    for (uint32_t t = threadIdx.x; t < nco_in; t += blockDim.x) {
+      fl_t c = ld_fl(coeff_in + t);
+      st_fl(coeff_out + 2 * t, fl_mul(c, u_inv));
+      st_fl(coeff_out + 2 * t + 1, fl_mul(c, u));
+    }
+    __syncthreads();
+  }
+  if (n <= 1) return;
+  const fl_t* coeff = do_fold ? coeff_out : coeff_in;
+  const uint32_t half = n / 2;
+  fl_t c[2];
+  c[0] = c[1] = fl_zero();
+  for (uint32_t i = threadIdx.x; i < half; i += blockDim.x) {
+    fl_t al = ld_fl(a + i), ar = ld_fl(a + half + i), bl = ld_fl(b + i), br = ld_fl(b + half + i);
+    c[0] = fl_add(c[0], fl_mul(al, br));
+    c[1] = fl_add(c[1], fl_mul(ar, bl));
+  }
+  block_sum_fl<2>(c, smem);
+  const size_t stride = (size_t)Rsize + 2;
+  (void)stride;
+  for (uint32_t g = threadIdx.x; g < Rsize; g += blockDim.x) {
+    uint32_t t = g / n, pos = g % n;
+    fl_t co = ld_fl(coeff + t);
+    if (pos >= half) {
+      st_fl(sL + g, fl_from_mont(fl_mul(ld_fl(a + (pos - half)), co)));
+      st_fl(sR + g, fl_zero());
+    } else {
+      st_fl(sR + g, fl_from_mont(fl_mul(ld_fl(a + half + pos), co)));
+      st_fl(sL + g, fl_zero());
+    }
+  }
+  if (threadIdx.x == 0) {
+    st_fl(sL + Rsize, fl_from_mont(blind_L));
+    st_fl(sL + Rsize + 1, fl_from_mont(c[0]));
+    st_fl(sR + Rsize, fl_from_mont(blind_R));
+    st_fl(sR + Rsize + 1, fl_from_mont(c[1]));
+  }
+}
+cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize, bool do_fold,
+                          fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR, cudaStream_t s) {
+  bullet_step_kernel<<<1, 1024, 0, s>>>(a, b, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv, blind_L, blind_R, sL, sR);
+  return SB_LAUNCHED();
+}
+__global__ void scale_from_mont_kernel(const fl_t* __restrict__ coeff, fl_t d, uint32_t n, fl_t* __restrict__ out) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    st_fl(out + i, fl_from_mont(fl_mul(ld_fl(coeff + i), d)));
+}
+cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s) {
+  scale_from_mont_kernel<<<grid_for(n, 128), 128, 0, s>>>(coeff, d, n, out);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ fixed-base MSM
+__device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {
+  niels_t n;
+  n.yplusx = ldg_fp(&p->yplusx);
+  n.yminusx = ldg_fp(&p->yminusx);
+  n.xy2d = ldg_fp(&p->xy2d);
+  return n;
+}
+// acc += k * B where B's window table starts at tb; k = canonical scalar at global address kp.
+// Signed radix-2^c digits in (-2^(c-1), 2^(c-1)]; zero digits cost nothing (vartime, like the
+// reference's vartime_multiscalar_mul).
+__device__ __forceinline__ void msm_accumulate(ge_t& acc, const niels_t* __restrict__ tb, const uint32_t* __restrict__ kp,
+                                               uint32_t c, uint32_t windows) {
+  uint32_t carry = 0;
+  for (uint32_t w = 0; w < windows; w++) {
+    int32_t d = msm_digit(kp, w, c, carry);
+    if (d != 0) {
+      bool neg = d < 0;
+      uint32_t mag = (uint32_t)(neg ? -d : d);
+      niels_t e = ldg_niels(tb + ((size_t)w << (c - 1)) + (mag - 1));
+      acc = ge_madd(acc, e, neg);
+    }
+  }
+}
+__global__ void __launch_bounds__(256) msm_fixed_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
+                                                        const fl_t* __restrict__ scalars, size_t stride, uint32_t n,
+                                                        const fl_t* __restrict__ extra_h, uint32_t h_index, ge_t* partial) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  ge_t* sm = reinterpret_cast<ge_t*>(smem_raw);
+  const uint32_t row = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
+  const size_t epb = (size_t)windows << (c - 1);
+  const uint32_t per = (n + nsplit - 1) / nsplit;
+  const uint32_t j0 = split * per, j1 = min(n, j0 + per);
+  ge_t acc = ge_identity();
+  for (uint32_t j = j0 + threadIdx.x; j < j1; j += blockDim.x)
+    msm_accumulate(acc, tbl + (size_t)j * epb, reinterpret_cast<const uint32_t*>(scalars + (size_t)row * stride + j), c, windows);
+  if (extra_h != nullptr && split == 0 && threadIdx.x == 0)
+    msm_accumulate(acc, tbl + (size_t)h_index * epb, reinterpret_cast<const uint32_t*>(extra_h + row), c, windows);
+  sm[threadIdx.x] = acc;
+  __syncthreads();
+  for (uint32_t o = blockDim.x >> 1; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sm[threadIdx.x] = ge_add(sm[threadIdx.x], sm[threadIdx.x + o]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = sm[0];
+}
+__global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit, uint8_t* __restrict__ out32) {
+  uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= rows) return;
+  ge_t acc = partial[(size_t)row * nsplit];
+  for (uint32_t s = 1; s < nsplit; s++) acc = ge_add(acc, partial[(size_t)row * nsplit + s]);
+  uint32_t w[8];
+  ge_compress(acc, w);
+  uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
+  o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+MsmPlan msm_plan(uint32_t rows, uint32_t n) {
+  MsmPlan p;
+  p.rows = rows;
+  p.n = n;
+  // enough blocks to cover the chip a few times over, never fewer than 64 terms per block
+  uint32_t want = (uint32_t)((kSMs * 4 + rows - 1) / (rows ? rows : 1));
+  uint32_t maxs = (n + 63) / 64;
+  if (want < 1) want = 1;
+  if (maxs < 1) maxs = 1;
+  p.splits = want < maxs ? want : maxs;
+  return p;
+}
+size_t msm_scratch_bytes(uint32_t rows, uint32_t n) {
+  MsmPlan p = msm_plan(rows, n);
+  return (size_t)rows * p.splits * sizeof(ge_t);
+}
+cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, const fl_t* extra_h,
+                      const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch, uint8_t* out32,
+                      cudaStream_t s) {
+  (void)extra_q;
+  (void)q_index;
+  if (!rows) return cudaSuccess;
+  MsmPlan p = msm_plan(rows, n);
+  uint32_t per = (n + p.splits - 1) / p.splits;
+  int block = per >= 256 ? 256 : per >= 128 ? 128 : 64;
+  dim3 grid(p.splits, rows);
+  msm_fixed_kernel<<<grid, block, block * sizeof(ge_t), s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index,
+                                                              reinterpret_cast<ge_t*>(scratch));
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  msm_finish_kernel<<<(rows + 63) / 64, 64, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ table build
+// thread per (base, window, chunk of CH multiples): tbl[base][w][m-1] = m * 2^(c*w) * G_base as affine Niels.
+static constexpr int kTblChunk = 64;
+__global__ void __launch_bounds__(64) msm_table_kernel(const fp_t* __restrict__ affine_xy, uint32_t nbases, uint32_t c,
+                                                       uint32_t windows, niels_t* __restrict__ tbl) {
+  const uint32_t epw = 1u << (c - 1);
+  const uint32_t ch = epw < (uint32_t)kTblChunk ? epw : (uint32_t)kTblChunk;
+  const uint32_t chunks = epw / ch;
+  size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  size_t total = (size_t)nbases * windows * chunks;
+  if (tid >= total) return;
+  uint32_t chunk = (uint32_t)(tid % chunks);
+  uint32_t w = (uint32_t)((tid / chunks) % windows);
+  uint32_t base = (uint32_t)(tid / ((size_t)chunks * windows));
+  ge_t P;
+  P.X = ldg_fp(affine_xy + 2 * (size_t)base);
+  P.Y = ldg_fp(affine_xy + 2 * (size_t)base + 1);
+  P.Z = fp_one();
+  P.T = fp_mul(P.X, P.Y);
+  for (uint32_t k = 0; k < c * w; k++) P = ge_double(P);
+  // M = (chunk*ch + 1) * P
+  uint32_t m0 = chunk * ch + 1;
+  ge_t M = ge_identity();
+  for (int bit = 15; bit >= 0; bit--) {
+    M = ge_double(M);
+    if ((m0 >> bit) & 1u) M = ge_add(M, P);
+  }
+  niels_t* slot = tbl + ((size_t)base * windows + w) * epw + (size_t)chunk * ch;
+  fp_t pre[kTblChunk];
+  fp_t acc = fp_one();
+  for (uint32_t k = 0; k < ch; k++) {
+    pre[k] = acc;
+    acc = fp_mul(acc, M.Z);
+    st_fp(&slot[k].yplusx, M.X);
+    st_fp(&slot[k].yminusx, M.Y);
+    st_fp(&slot[k].xy2d, M.Z);
+    M = ge_add(M, P);
+  }
+  fp_t inv = fp_invert(acc);
+  for (int k = (int)ch - 1; k >= 0; k--) {
+    fp_t X = slot[k].yplusx, Y = slot[k].yminusx, Z = slot[k].xy2d;
+    fp_t zi = fp_mul(inv, pre[k]);
+    inv = fp_mul(inv, Z);
+    niels_t e = niels_from_affine(fp_mul(X, zi), fp_mul(Y, zi));
+    st_fp(&slot[k].yplusx, e.yplusx);
+    st_fp(&slot[k].yminusx, e.yminusx);
+    st_fp(&slot[k].xy2d, e.xy2d);
+  }
+}
+cudaError_t msm_table_build(MsmTable& t, const uint8_t* affine_xy_host, uint32_t nbases, uint32_t c, cudaStream_t s) {
+  t.nbases = nbases;
+  t.c = c;
+  t.windows = msm_windows(c);
+  size_t bytes = (size_t)nbases * t.entries_per_base() * sizeof(niels_t);
+  cudaError_t e = cudaMalloc(&t.tbl, bytes);
+  if (e != cudaSuccess) return e;
+  fp_t* d_xy = nullptr;
+  e = cudaMalloc(&d_xy, (size_t)nbases * 64);
+  if (e != cudaSuccess) return e;
+  e = cudaMemcpyAsync(d_xy, affine_xy_host, (size_t)nbases * 64, cudaMemcpyHostToDevice, s);
+  if (e != cudaSuccess) return e;
+  uint32_t epw = 1u << (c - 1), ch = epw < (uint32_t)kTblChunk ? epw : (uint32_t)kTblChunk;
+  size_t total = (size_t)nbases * t.windows * (epw / ch);
+  msm_table_kernel<<<(unsigned)((total + 63) / 64), 64, 0, s>>>(d_xy, nbases, c, t.windows, t.tbl);
+  e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  e = cudaStreamSynchronize(s);
+  cudaFree(d_xy);
+  return e;
+}
+void msm_table_free(MsmTable& t) {
+  if (t.tbl) cudaFree(t.tbl);
+  t.tbl = nullptr;
+}
+
+}  // namespace sb

@@ -121,6 +121,12 @@ def pt_add(a, b):
     return bytes(o) if ok else None
 
 
+def pt_affine(a):
+    o = _out(64)
+    ok = lib().orc_pt_affine(_buf(a), o)
+    return bytes(o) if ok else None
+
+
 def pt_decompress_ok(a):
     return bool(lib().orc_pt_decompress_ok(_buf(a)))
 

@@ -1,0 +1,315 @@
+"""Parity of every sm_100a kernel and of the whole NIZK::prove against the CPU oracle.
+
+All calls go through the C ABI (include/spartan_b200.h, spartan_b200_kernels.h).
+Bar: bit-exact (integer / byte work).
+"""
+import ctypes as C
+import random
+
+import pytest
+
+import oracle_lib as O
+from common import ELL, LABEL, TAPE_SEED, canon, mont, rand_scalars
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def sb():
+    import otti_b200
+    L = otti_b200.lib()
+    assert L.sb200_init(0) == 0, L.sb200_last_error()
+    return otti_b200
+
+
+def _buf(b):
+    return (C.c_uint8 * max(len(b), 1)).from_buffer_copy(bytes(b)) if len(b) else (C.c_uint8 * 1)()
+
+
+def _out(n):
+    return (C.c_uint8 * max(n, 1))()
+
+
+EDGE = [0, 1, 2, ELL - 1, ELL - 2, 2**252, 2**252 - 1, 2**128, 2**64 - 1, (ELL - 1) // 2]
+
+
+def test_fl_binops(sb):
+    """Scalar add/sub/mul on the device == ristretto255.rs:702-755 (via the oracle), incl. edge values."""
+    n = 4096
+    xs = EDGE + rand_scalars(n - len(EDGE), 1)
+    ys = list(reversed(EDGE)) + rand_scalars(n - len(EDGE), 2)
+    a, b = mont(xs), mont(ys)
+    for op, name in ((0, "add"), (1, "sub"), (2, "mul")):
+        o = _out(32 * n)
+        assert sb.lib().sb200_k_fl_binop(op, _buf(a), _buf(b), o, C.c_size_t(n)) == 0
+        got = bytes(o)
+        for i in range(0, n, 97):
+            assert got[32 * i:32 * i + 32] == O.fl_binop(name, a[32 * i:32 * i + 32], b[32 * i:32 * i + 32]), (name, i)
+        f = {"add": lambda x, y: (x + y) % ELL, "sub": lambda x, y: (x - y) % ELL, "mul": lambda x, y: x * y % ELL}[name]
+        assert got == mont([f(x, y) for x, y in zip(xs, ys)])
+
+
+def test_to_from_mont_and_canonicity(sb):
+    """Scalar::from_bytes / to_bytes (ristretto255.rs:398-438) incl. rejection of values >= l."""
+    xs = EDGE + rand_scalars(1000, 3)
+    o = _out(32 * len(xs))
+    bad = C.c_int(7)
+    assert sb.lib().sb200_k_to_mont(_buf(canon(xs)), o, C.c_size_t(len(xs)), C.byref(bad)) == 0
+    assert bad.value == 0
+    want, _ = O.fl_batch_from_bytes(canon(xs))
+    assert bytes(o) == want
+    back = _out(32 * len(xs))
+    assert sb.lib().sb200_k_from_mont(o, back, C.c_size_t(len(xs))) == 0
+    assert bytes(back) == canon(xs)
+    for v in (ELL, ELL + 1, 2**256 - 1):
+        assert sb.lib().sb200_k_to_mont(_buf(canon([5, v, 6])), _out(96), C.c_size_t(3), C.byref(bad)) == 0
+        assert bad.value == 1
+
+
+@pytest.mark.parametrize("ell", [0, 1, 2, 3, 7, 8, 9, 10, 13, 16])
+def test_eq_evals(sb, ell):
+    """EqPolynomial::evals (dense_mlpoly.rs:67-83)."""
+    r = mont(rand_scalars(ell, 10 + ell))
+    o = _out(32 << ell)
+    assert sb.lib().sb200_k_eq_evals(_buf(r), ell, o) == 0
+    assert bytes(o) == O.eq_evals(r)
+
+
+def _random_instance(num_cons, num_vars, num_inputs, seed, max_row=6, heavy=True):
+    """Ragged R1CS: empty rows, multi-entry rows, duplicate (row,col) entries, a heavy constant column."""
+    rng = random.Random(seed)
+    ncols = num_vars + 1 + num_inputs
+    mats = []
+    for m in range(3):
+        M = []
+        for row in range(num_cons):
+            k = rng.choice([0, 1, 1, 1, 2, 3, max_row])
+            for _ in range(k):
+                col = rng.randrange(ncols)
+                if heavy and rng.random() < 0.3:
+                    col = num_vars  # the constant-1 column
+                val = rng.choice([1, ELL - 1, 2, rng.randrange(ELL), rng.randrange(2**32)])
+                M.append((row, col, int(val).to_bytes(32, "little")))
+        if M:
+            M.append(M[0])  # duplicate entry: contributions must add up
+        mats.append(M)
+    return mats
+
+
+@pytest.mark.parametrize("dims", [(8, 8, 3), (37, 20, 5), (256, 256, 10), (1000, 700, 17), (1, 0, 3), (2, 1, 0)])
+def test_multiply_vec_and_eval_table(sb, dims):
+    """R1CSInstance::multiply_vec and compute_eval_table_sparse+combine on ragged instances
+    (r1csinstance.rs:248-278, sparse_mlpoly.rs:452-483, r1csproof.rs:268-279)."""
+    nc, nv, ni = dims
+    A, B, Cm = _random_instance(nc, nv, ni, 100 + nc)
+    oi = O.Instance.new(nc, nv, ni, A, B, Cm)
+    pi = sb.Instance.new(nc, nv, ni, A, B, Cm)
+    assert (pi.num_cons, pi.num_vars, pi.num_inputs) == (oi.num_cons, oi.num_vars, oi.num_inputs)
+    z = mont(rand_scalars(2 * oi.num_vars, 5))
+    oa, ob, oc = oi.multiply_vec(z)
+    ga, gb, gc = _out(len(oa)), _out(len(oa)), _out(len(oa))
+    assert sb.lib().sb200_k_multiply_vec(pi.h, _buf(z), ga, gb, gc) == 0
+    assert (bytes(ga), bytes(gb), bytes(gc)) == (oa, ob, oc)
+    e = mont(rand_scalars(oi.num_cons, 6))
+    rabc = mont(rand_scalars(3, 7))
+    want = oi.eval_table_abc(e, rabc)
+    got = _out(len(want))
+    assert sb.lib().sb200_k_eval_table_abc(pi.h, _buf(e), _buf(rabc), got) == 0
+    assert bytes(got) == want
+
+
+@pytest.mark.parametrize("ntab", [4, 2])
+@pytest.mark.parametrize("logn", [1, 2, 5, 9, 12, 15])
+def test_sumcheck_rounds(sb, ntab, logn):
+    """A full chain of fused bind+evaluate rounds == bound_poly_var_top + round evaluations of the
+    reference (sumcheck.rs:453-484, 618-674; dense_mlpoly.rs:214-221)."""
+    n = 1 << logn
+    tabs = [mont(rand_scalars(n, 20 + k)) for k in range(ntab)]
+    dev = [_buf(t) for t in tabs]
+    ptrs = (C.c_void_p * ntab)(*[C.cast(d, C.c_void_p) for d in dev])
+    ev = _out(96)
+    assert sb.lib().sb200_k_sumcheck_round(ptrs, ntab, C.c_size_t(n), None, ev) == 0
+    e = O.sumcheck_round(tabs)
+    assert bytes(ev)[:64] == e[0] + e[1]
+    if ntab == 4:
+        assert bytes(ev)[64:] == e[2]
+    length = n
+    rng = random.Random(logn)
+    while length > 1:
+        r = mont([rng.randrange(ELL)])
+        assert sb.lib().sb200_k_sumcheck_round(ptrs, ntab, C.c_size_t(length), _buf(r), ev) == 0
+        tabs = [O.bind_top(t, r) for t in tabs]
+        length //= 2
+        for d, t in zip(dev, tabs):
+            assert bytes(d)[:32 * length] == t
+        if length > 1:
+            e = O.sumcheck_round(tabs)
+            assert bytes(ev)[:64] == e[0] + e[1]
+            if ntab == 4:
+                assert bytes(ev)[64:] == e[2]
+
+
+@pytest.mark.parametrize("shape", [(1, 2), (2, 2), (4, 8), (16, 16), (64, 128), (256, 256)])
+def test_poly_bound_and_dot(sb, shape):
+    """DensePolynomial::bound and compute_dotproduct (dense_mlpoly.rs:205-212, nizk/mod.rs:430-433)."""
+    Ls, Rs = shape
+    Z = mont(rand_scalars(Ls * Rs, 31))
+    Lv = mont(rand_scalars(Ls, 32))
+    o = _out(32 * Rs)
+    assert sb.lib().sb200_k_poly_bound(_buf(Z), C.c_size_t(Ls * Rs), _buf(Lv), C.c_size_t(Ls), o) == 0
+    assert bytes(o) == O.poly_bound(Z, Lv)
+    b = mont(rand_scalars(Rs, 33))
+    d = _out(32)
+    assert sb.lib().sb200_k_dot(o, _buf(b), C.c_size_t(Rs), d) == 0
+    assert bytes(d) == O.dot(bytes(o), b)
+
+
+@pytest.mark.parametrize("nv", [2, 16, 64, 1024])
+def test_generators_and_commit_rows(sb, nv):
+    """MultiCommitGens::new derivation (commitments.rs:15-58) and commit_inner rows
+    (dense_mlpoly.rs:163-176) incl. zero, small and maximal scalars."""
+    og = O.Gens(nv, nv, 1)
+    pg = sb.NIZKGens.new(nv, nv, 1)
+    n = sb.lib().sb200_k_gens_n(pg.h)
+    assert n == og.n
+    for which, cnt in ((0, min(n, 8)), (1, 1), (2, 1), (3, 3), (4, 1), (5, 4), (6, 1)):
+        for i in range(cnt):
+            o = _out(32)
+            assert sb.lib().sb200_k_gens_point(pg.h, which, C.c_size_t(i), o) == 0
+            assert bytes(o) == og.point(which, i), (which, i)
+    ell = nv.bit_length() - 1
+    Ls = 1 << (ell // 2)
+    xs = rand_scalars(nv, 41)
+    for i, v in enumerate([0, 1, ELL - 1, 2**252, 255, 256, 2**64]):
+        if i < nv:
+            xs[i] = v
+    blinds = rand_scalars(Ls, 42)
+    blinds[0] = 0
+    o = _out(32 * Ls)
+    assert sb.lib().sb200_k_commit_rows(pg.h, _buf(canon(xs)), C.c_size_t(nv), _buf(canon(blinds)), C.c_size_t(Ls), o) == 0
+    assert bytes(o) == og.commit_rows(mont(xs), mont(blinds))
+    c = _out(32)
+    assert sb.lib().sb200_k_commit_scalar(pg.h, _buf(canon([xs[-1]])), _buf(canon([blinds[-1]])), c) == 0
+    assert bytes(c) == O.pt_msm(mont([xs[-1], blinds[-1]]), og.point(2) + og.point(1))
+
+
+def test_merlin(sb):
+    o = _out(32)
+    sb.lib().sb200_k_merlin(_buf(b"test protocol"), C.c_size_t(13), b"some label", _buf(b"some data"), C.c_size_t(9),
+                            b"challenge", o, C.c_size_t(32))
+    assert bytes(o).hex() == "d5a21972d0d5fe320c0d263fac7fffb8145aa640af6e9bca177c03c7efcf0615"
+
+
+@pytest.mark.parametrize("s", [1, 2, 3, 4, 5, 6, 8, 10, 12])
+def test_nizk_prove_byte_identical_synthetic(sb, s):
+    """NIZK::prove on produce_synthetic_r1cs: proof bytes == oracle's, oracle verify accepts."""
+    n = 1 << s
+    ni = min(10, n - 1)
+    oi, ov, oin = O.Instance.synthetic(n, n, ni, 0x0771)
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, ni, 0x0771)
+    assert (pv.data, pin.data) == (ov, oin)
+    assert pi.is_sat(pv, pin)
+    og = O.Gens(n, n, ni)
+    pg = sb.NIZKGens.new(n, n, ni)
+    want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == want
+    assert O.nizk_verify(oi, oin, og, LABEL, proof.to_bytes()) == 0
+
+
+@pytest.mark.parametrize("dims", [(37, 20, 5), (1, 0, 3), (300, 100, 64), (64, 600, 2), (5, 3, 8)])
+def test_nizk_prove_ragged(sb, dims):
+    """Non-power-of-two sizes (padding of Instance::new / Assignment::pad), num_vars < num_inputs+1,
+    heavy columns, duplicate entries: find a satisfying assignment by construction, prove, compare."""
+    nc, nv, ni = dims
+    rng = random.Random(nc * 1000 + nv)
+    vars_ = [rng.randrange(ELL) for _ in range(nv)]
+    inputs = [rng.randrange(ELL) for _ in range(ni)]
+    z = vars_ + [1] + inputs
+    ncols = len(z)
+    A, B, Cm = [], [], []
+    for row in range(nc):
+        ra = [(rng.randrange(ncols), rng.choice([1, 2, ELL - 1, rng.randrange(ELL)])) for _ in range(rng.choice([1, 2, 3]))]
+        rb = [(rng.randrange(ncols), rng.choice([1, rng.randrange(2**20)])) for _ in range(rng.choice([1, 2]))]
+        if row % 7 == 0:
+            ra.append((nv, 5))  # the constant column
+        az = sum(v * z[c] for c, v in ra) % ELL
+        bz = sum(v * z[c] for c, v in rb) % ELL
+        # C row: one entry on the constant column carrying az*bz
+        A += [(row, c, v.to_bytes(32, "little")) for c, v in ra]
+        B += [(row, c, v.to_bytes(32, "little")) for c, v in rb]
+        Cm.append((row, nv, (az * bz % ELL).to_bytes(32, "little")))
+    oi = O.Instance.new(nc, nv, ni, A, B, Cm)
+    pi = sb.Instance.new(nc, nv, ni, A, B, Cm)
+    vb, ib = canon(vars_), canon(inputs)
+    assert oi.is_sat(vb, ib) == 1
+    pv, pin = sb.VarsAssignment.new(vb), sb.InputsAssignment.new(ib)
+    assert pi.is_sat(pv, pin)
+    og = O.Gens(nc, nv, ni)
+    pg = sb.NIZKGens.new(nc, nv, ni)
+    want = O.nizk_prove(oi, vb, ib, og, LABEL, TAPE_SEED)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == want
+    assert O.nizk_verify(oi, ib, og, LABEL, proof.to_bytes()) == 0
+    # an unsatisfying assignment is detected
+    bad = canon([(vars_[0] + 1) % ELL] + vars_[1:]) if nv else None
+    if bad is not None and any(c == 0 for _, c, _ in A + B):
+        assert not pi.is_sat(sb.VarsAssignment.new(bad), pin)
+
+
+def test_error_behaviour(sb):
+    """check_r1cs_invalid_index / check_r1cs_invalid_scalar (lib.rs:607-650) and prove's asserts."""
+    zero = bytes(32)
+    with pytest.raises(sb.R1CSError) as e:
+        sb.Instance.new(4, 8, 1, [(0, 0, zero)], [(100, 1, zero)], [(1, 1, zero)])
+    assert e.value.kind == "InvalidIndex"
+    larger = bytes([3, 0, 0, 0, 255, 255, 255, 255, 254, 91, 254, 255, 2, 164, 189, 83, 5, 216, 161, 9, 8, 216, 57, 51, 72,
+                    125, 157, 41, 83, 167, 237, 115])
+    with pytest.raises(sb.R1CSError) as e:
+        sb.Instance.new(4, 8, 1, [(0, 0, zero)], [(1, 1, larger)], [(1, 1, zero)])
+    assert e.value.kind == "InvalidScalar"
+    with pytest.raises(sb.R1CSError) as e:
+        sb.VarsAssignment.new([larger])
+    assert e.value.kind == "InvalidScalar"
+    inst, v, i = sb.Instance.produce_synthetic_r1cs(16, 16, 3, 1)
+    gens = sb.NIZKGens.new(16, 16, 3)
+    with pytest.raises(AssertionError):  # wrong number of inputs: the reference asserts z.len() == num_cols
+        sb.NIZK.prove(inst, v, sb.InputsAssignment.new(i.data[:64]), gens, sb.Transcript.new(LABEL), TAPE_SEED)
+    with pytest.raises(sb.R1CSError) as e:
+        inst.is_sat(v, sb.InputsAssignment.new(i.data[:64]))
+    assert e.value.kind == "InvalidNumberOfInputs"
+
+
+def test_test_padded_constraints(sb):
+    """lib.rs:653-731 test_padded_constraints: 1 constraint, 0 vars, 3 inputs (NIZK part)."""
+    one = (1).to_bytes(32, "little")
+    A = [(0, 2, one)]
+    B = [(0, 2, one)]
+    Cm = [(0, 1, one), (0, 0, (ELL - 13).to_bytes(32, "little")), (0, 3, (ELL - 1).to_bytes(32, "little"))]
+    inputs = canon([16, 1, 2])
+    pi = sb.Instance.new(1, 0, 3, A, B, Cm)
+    oi = O.Instance.new(1, 0, 3, A, B, Cm)
+    pv, pin = sb.VarsAssignment.new(b""), sb.InputsAssignment.new(inputs)
+    assert pi.is_sat(pv, pin)
+    pg, og = sb.NIZKGens.new(1, 0, 3), O.Gens(1, 0, 3)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == O.nizk_prove(oi, b"", inputs, og, LABEL, TAPE_SEED)
+    assert O.nizk_verify(oi, inputs, og, LABEL, proof.to_bytes()) == 0
+
+
+def test_transcript_state_advances_and_tape_randomness(sb):
+    """The caller's transcript is mutated in place (lib.rs:497-504); with tape_seed=None two proofs differ
+    (random.rs:11-19) yet both verify."""
+    inst, v, i = sb.Instance.produce_synthetic_r1cs(64, 64, 5, 9)
+    oi, ov, oin = O.Instance.synthetic(64, 64, 5, 9)
+    gens, og = sb.NIZKGens.new(64, 64, 5), O.Gens(64, 64, 5)
+    t = sb.Transcript.new(LABEL)
+    p1 = sb.NIZK.prove(inst, v, i, gens, t, TAPE_SEED)
+    fresh = sb.Transcript.new(LABEL)
+    assert t.challenge_bytes(b"x", 16) != fresh.challenge_bytes(b"x", 16)
+    pa = sb.NIZK.prove(inst, v, i, gens, sb.Transcript.new(LABEL))
+    pb = sb.NIZK.prove(inst, v, i, gens, sb.Transcript.new(LABEL))
+    assert pa.to_bytes() != pb.to_bytes()
+    for p in (p1, pa, pb):
+        assert O.nizk_verify(oi, oin, og, LABEL, p.to_bytes()) == 0
+    assert p1.r1cs_sat_proof_len == len(p1.to_bytes()) - (8 + 32 * 6) - (8 + 32 * 7)
