@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""bench.py -- Spartan NIZK prove throughput (constraints/s) on B200, per the driver contract.
+
+A "step" is one NIZK::prove of one synthetic R1CS (Instance::produce_synthetic_r1cs,
+r1csinstance.rs:136-214; 10 inputs, one non-zero per row and matrix, uniform 253-bit witness),
+generators and instance built outside the timed region like benches/nizk.rs:27-39.
+
+  value   witness already resident in HBM when the timed region starts
+  e2e     the same prove through the public API (otti_b200.NIZK.prove) from PINNED host memory:
+          host->device copy of the witness and device->host read of the proof inside the timed region
+  N > 1   one process per GPU, each proving its own instance (independent proofs are the natural
+          data-parallel unit of Otti's run.py loop over datasets); no data-path collective; weak scaling.
+
+--impl reference times the CPU restatement of the reference prover (oracle/, "port": the real
+curve25519-dalek prover is Rust and cannot be built in this image) with all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+LABEL = b"nizk_example"
+TAPE = bytes(range(64))
+SEED = 0x0771
+NUM_INPUTS = 10
+README_2_20_CONSTRAINTS_PER_S = (1 << 20) / 4.5140  # Spartan/README.md:365-377 (1 core, i7-1065G7)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--log-size", type=int, default=16, help="log2 of constraints = vars (configs[1] = 16)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md:70-72)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.p = gpu, None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "of measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "of fallback (B200_PROFILING.md)"
+
+
+def run_reference(args, rank, world):
+    """CPU restatement of the reference prover on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    import oracle_lib as O
+    s = min(args.log_size, 18)  # bounded sample: throughput in constraints/s is size-independent to first order (O(N) prover)
+    n = 1 << s
+    threads = host_threads()
+    inst, vars_, inputs = O.Instance.synthetic(n, n, NUM_INPUTS, SEED)
+    gens = O.Gens(n, n, NUM_INPUTS)
+    for _ in range(min(args.warmup, 1)):
+        O.nizk_prove(inst, vars_, inputs, gens, LABEL, TAPE, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.nizk_prove(inst, vars_, inputs, gens, LABEL, TAPE, threads)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = "%d full proves of synthetic R1CS 2^%d on %d host threads (commitment rows threaded like the reference's `multicore` feature)" % (
+        args.steps, s, threads)
+    line = {
+        "impl": "reference", "metric": "spartan_nizk_prove_constraints_per_s", "value": value, "unit": "constraints/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u256 (F_l 253-bit / F_p 255-bit integers)",
+        "data": "synthetic", "config": {"workload": "synthetic Spartan R1CS 2^%d constraints = vars, 10 inputs, NIZK::prove" % args.log_size,
+                                        "sample_log_size": s},
+        "cpu_baseline": {"value": value, "unit": "constraints/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "constraints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import otti_b200 as sb
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    assert sb.lib().sb200_init(local_rank) == 0, sb.lib().sb200_last_error()
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    s = args.log_size
+    n = 1 << s
+    inst, vars_, inputs = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED + rank, pinned=True)
+    t0 = time.perf_counter()
+    gens = sb.NIZKGens.new(n, n, NUM_INPUTS)
+    torch.cuda.synchronize()
+    gens_s = time.perf_counter() - t0
+
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def flush_l2(i):
+        flush_buf.fill_(i & 0xFF)
+        torch.cuda.synchronize()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    proof = None
+    for i in range(args.warmup):
+        proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE)
+    ext = torch.cuda.ExternalStream(inst.stream)
+
+    def timed(resident):
+        """K steps, each bracketed by CUDA events on the stream the kernels are launched on."""
+        nonlocal proof
+        total_ms, launches, prof = 0.0, 0, None
+        for i in range(args.steps):
+            flush_l2(i)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext)
+            proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE, resident=resident)
+            e1.record(ext)
+            e1.synchronize()
+            total_ms += e0.elapsed_time(e1)
+            prof = sb.NIZK.last_profile()
+            launches += int(prof["kernel_launches"])
+        return total_ms, launches, prof
+
+    sampler = ClockSampler(local_rank)
+    inst.upload_witness(gens, vars_)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    res_ms, launches, prof = timed(True)
+    barrier()
+    e2e_ms, _, prof_e2e = timed(False)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([res_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    res_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    value = world * n * args.steps / (res_ms * 1e-3)
+    e2e_value = world * n * args.steps / (e2e_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (commitment MSM), from CUDA events inside the timed region
+    ell = s
+    Ls, Rs = 1 << (ell // 2), 1 << (ell - ell // 2)
+    c = int(os.environ.get("SB200_MSM_WINDOW", "8"))
+    W = 252 // c + 1
+    terms = n + Ls
+    k_s = prof["msm_commit_kernel"]
+    alg_bytes = terms * 32 + terms * W * (1 - 2.0 ** -c) * 96  # scalars + one 96-byte table entry per non-zero digit
+    hbm_peak, which = measured_peaks()
+    achieved = alg_bytes / k_s / 1e9 if k_s > 0 else 0.0
+    mul32 = terms * W * 7 * 64  # 7 F_p multiplications of 8x8 limbs per mixed add
+    sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    int_peak = 148 * 64 * sm_mhz * 1e6  # IMAD lanes/clk/SM (B300_MICROARCH.md:85) at the sampled SM clock
+    roofline = {
+        "kernel": "msm_fixed_kernel (commitment rows, %d x %d)" % (Ls, Rs), "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+        "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": which,
+        "kernel_ms": 1e3 * k_s, "share_of_step": k_s / (res_ms * 1e-3 / args.steps),
+        "int_pipe": {"achieved_gmul32_per_s": mul32 / k_s / 1e9 if k_s > 0 else 0.0, "peak_gimad_per_s": int_peak / 1e9,
+                     "frac": (mul32 / k_s) / int_peak if k_s > 0 else 0.0,
+                     "note": "the kernel's real limiter: 255-bit modular products on the IMAD pipe (DESIGN.md)"},
+        "hbm_kernel_sample": {"kernel": "sc_cubic_kernel<false> (round 0: 4 tables x 32 B x 2^%d read)" % s,
+                              "achieved": 4 * 32 * n / prof["sc_cubic_round0_kernel"] / 1e9 if prof["sc_cubic_round0_kernel"] > 0 else 0.0,
+                              "unit": "GB/s", "kernel_ms": 1e3 * prof["sc_cubic_round0_kernel"]},
+    }
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        import oracle_lib as O
+        sb_s = min(s, 18)
+        nb = 1 << sb_s
+        oi, ov, oin = O.Instance.synthetic(nb, nb, NUM_INPUTS, SEED)
+        og = O.Gens(nb, nb, NUM_INPUTS)
+        t0 = time.perf_counter()
+        want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE, 1)
+        t1 = time.perf_counter()
+        threads = host_threads()
+        O.nizk_prove(oi, ov, oin, og, LABEL, TAPE, threads)
+        t2 = time.perf_counter()
+        parity = (want == proof.to_bytes()) if sb_s == s else None
+        cpu_baseline = {
+            "value": nb / (t1 - t0), "unit": "constraints/s", "cores": 1, "kind": "port",
+            "sample": "1 full prove of synthetic R1CS 2^%d, CPU restatement of the reference (not curve25519-dalek, no AVX2 point backend)" % sb_s,
+            "all_threads": {"value": nb / (t2 - t1), "cores": threads},
+            "proof_bytes_equal_gpu": parity,
+            "published_reference": {"value": README_2_20_CONSTRAINTS_PER_S, "unit": "constraints/s",
+                                    "note": "Spartan/README.md:365-377, 2^20, 1 core i7-1065G7 (other hardware)"},
+        }
+
+    line = {
+        "metric": "spartan_nizk_prove_constraints_per_s", "value": value, "unit": "constraints/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": res_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": (value / README_2_20_CONSTRAINTS_PER_S) if (s == 20 and world == 1) else None,
+        "dtype": "u256 (F_l 253-bit / F_p 255-bit integers)", "data": "synthetic",
+        "config": {"workload": "synthetic Spartan R1CS 2^%d constraints = vars, 10 inputs, NIZK::prove%s" % (
+            s, " (configs[1])" if s == 16 else ""), "per_gpu": "one independent proof per GPU per step", "l2": "256 MiB flush between timed steps",
+            "msm_window_bits": c, "gens_build_s_untimed": gens_s, "proof_bytes": len(proof.to_bytes())},
+        "prove_time_s": res_ms * 1e-3 / args.steps,
+        "phases_ms": {k: 1e3 * prof[k] for k in ("polycommit", "prove_sc_phase_one", "prove_sc_phase_two", "polyeval", "host_fiat_shamir")},
+        "e2e": {"value": e2e_value, "unit": "constraints/s", "h2d_bytes_per_step": int(prof_e2e["h2d_bytes"]),
+                "d2h_bytes_per_step": int(prof_e2e["d2h_bytes"]), "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -145,6 +145,7 @@ void sb200_gens_free(sb200_gens* gens);
  *                  Scalar::random(OsRng) that seeds RandomTape (random.rs:11-19);
  *                  NULL draws them from the OS like the reference.
  *  comm            NULL, or the exchange hook when the proof is sharded over several GPUs
+ *  vars32          host pointer, or NULL to use the witness placed by sb200_witness_upload
  *  proof_out/len   bincode(NIZK); release with sb200_free
  * SB200_ERR_ASSERT where the reference asserts (inputs.len() >= vars.len(), r1csproof.rs:153). */
 int sb200_nizk_prove(const sb200_instance* inst, const uint8_t* vars32, uint64_t n_vars, const uint8_t* inputs32,
@@ -160,9 +161,19 @@ int sb200_nizk_verify(const sb200_instance* inst, const uint8_t* inputs32, uint6
                       const uint8_t* proof, size_t proof_len);
 
 /* Timer scopes of the last prove on this thread, seconds               timer.rs, r1csproof.rs:155-307
- * out[0..7] = polycommit, prove_sc_phase_one, prove_sc_phase_two, polyeval,
- *             total, h2d (inside total), host Fiat-Shamir time (inside total), kernel launches */
-int sb200_last_prove_profile(double out[8]);
+ * out[0..9] = polycommit, prove_sc_phase_one, prove_sc_phase_two, polyeval, total,
+ *             witness h2d (inside total), critical-path host Fiat-Shamir time (inside total),
+ *             kernel launches, host->device bytes, device->host bytes,
+ *             device time of the commitment MSM kernel, device time of the first cubic sum-check kernel
+ *             (both from CUDA events on the instance's stream) */
+int sb200_last_prove_profile(double out[12]);
+
+/* Measurement helpers (no reference counterpart).
+ * sb200_witness_upload places vars in HBM so that a following sb200_nizk_prove(vars32 = NULL, same
+ * n_vars) starts with its input resident; sb200_instance_stream returns the cudaStream_t (as an
+ * integer) the instance's kernels are launched on, for CUDA-event timing on that stream. */
+int sb200_witness_upload(const sb200_instance* inst, const sb200_gens* gens, const uint8_t* vars32, uint64_t n_vars);
+uint64_t sb200_instance_stream(const sb200_instance* inst);
 
 void sb200_free(void* p);
 const char* sb200_last_error(void);

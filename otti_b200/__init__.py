@@ -58,6 +58,7 @@ def lib():
         L.sb200_last_error.restype = C.c_char_p
         L.sb200_k_gens_n.restype = C.c_size_t
         L.sb200_k_launch_count.restype = C.c_uint64
+        L.sb200_instance_stream.restype = C.c_uint64
         _lib = L
     return _lib
 
@@ -83,6 +84,8 @@ def _ptr(obj):
         return C.c_void_p(obj.data_ptr()), obj
     if hasattr(obj, "ctypes"):  # numpy
         return C.c_void_p(obj.ctypes.data), obj
+    if isinstance(obj, bytes):  # no copy: the bytes object itself is the keep-alive
+        return C.cast(C.c_char_p(obj), C.c_void_p), obj
     b = (C.c_uint8 * max(len(obj), 1)).from_buffer_copy(bytes(obj)) if len(obj) else (C.c_uint8 * 1)()
     return C.cast(b, C.c_void_p), b
 
@@ -224,6 +227,15 @@ class Instance:
             v, i = bytes(vbuf)[:num_vars * 32], bytes(ibuf)[:num_inputs * 32]
         return Instance(h), Assignment(v, num_vars), Assignment(i, num_inputs)
 
+    def upload_witness(self, gens, vars_):
+        """Place the witness in HBM (bench.py's "inputs already resident" measurement)."""
+        vp, vk = _ptr(vars_.data)
+        _check(lib().sb200_witness_upload(self.h, gens.h, vp, C.c_uint64(vars_.n)))
+
+    @property
+    def stream(self):
+        return int(lib().sb200_instance_stream(self.h))
+
     def is_sat(self, vars_, inputs):
         """`Instance::is_sat` (lib.rs:228-257) -> bool; raises R1CSError("InvalidNumberOfInputs")."""
         vp, vk = _ptr(vars_.data)
@@ -264,10 +276,10 @@ class NIZK:
         self.bytes = proof_bytes
 
     @staticmethod
-    def prove(inst, vars_, inputs, gens, transcript, tape_seed64=None):
+    def prove(inst, vars_, inputs, gens, transcript, tape_seed64=None, resident=False):
         """`NIZK::prove(&inst, vars, &inputs, &gens, &mut transcript)` (lib.rs:493-535).
         tape_seed64 (64 bytes) pins the RandomTape seed for reproducible proofs; None = OS randomness."""
-        vp, vk = _ptr(vars_.data)
+        vp, vk = (None, None) if resident else _ptr(vars_.data)
         ip, ik = _ptr(inputs.data)
         sp, sk = _ptr(tape_seed64)
         if tape_seed64 is not None and len(tape_seed64) != 64:
@@ -308,8 +320,8 @@ class NIZK:
     @staticmethod
     def last_profile():
         """Timer scopes of the last prove (timer.rs; r1csproof.rs:155-307)."""
-        d = (C.c_double * 8)()
+        d = (C.c_double * 12)()
         lib().sb200_last_prove_profile(d)
         keys = ["polycommit", "prove_sc_phase_one", "prove_sc_phase_two", "polyeval", "total", "h2d", "host_fiat_shamir",
-                "kernel_launches"]
+                "kernel_launches", "h2d_bytes", "d2h_bytes", "msm_commit_kernel", "sc_cubic_round0_kernel"]
         return dict(zip(keys, list(d)))

@@ -32,7 +32,7 @@ struct MsmPlan {
 MsmPlan msm_plan(uint32_t rows, uint32_t n);
 cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n,
                       const fl_t* extra_h, const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch,
-                      uint8_t* out32, cudaStream_t s);
+                      uint8_t* out32, cudaStream_t s, cudaEvent_t* ev = nullptr);  // ev[0..1] bracket the main kernel
 size_t msm_scratch_bytes(uint32_t rows, uint32_t n);
 
 // ---- F_l vector kernels -------------------------------------------------------------------
@@ -79,6 +79,9 @@ cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rs
 size_t bound_L_tmp_scalars(uint32_t Lsize, uint32_t Rsize);
 // out[0] = <a, b>   (n <= 2^16, one block)                            (nizk/mod.rs:305-308)
 cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cudaStream_t s);
+
+// w.result[m] = <e, y_m> for the three vectors (verifier's multi_evaluate)   (sparse_mlpoly.rs:412-450)
+cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC, size_t n, const ScWork& w, cudaStream_t s);
 
 // Bullet reduction scalar side (nizk/bullet.rs:71-118), see kernels.cu
 cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize,

@@ -62,6 +62,7 @@ struct SparseDev {  // CSR (by row) or CSC (by column) of the three matrices
 
 struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   bool ready = false;
+  uint64_t resident_vars = ~0ull;  // witness length placed by sb200_witness_upload
   DevBuf<sb::fl_t> vars_canon, varsM, z, abc, T, A, B, C, eq_tmp, sc_partials, small, blinds, bound_tmp, LZ, bl_a, bl_b,
       coeff0, coeff1, srows;
   DevBuf<unsigned int> counter;
@@ -70,7 +71,9 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   uint8_t* pinned = nullptr;  // host staging
   size_t pinned_bytes = 0;
   cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // [0,1] commit MSM kernel, [2,3] first cubic round
   ~Workspace() {
+    for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);
     if (pinned) cudaFreeHost(pinned);
     if (stream) cudaStreamDestroy(stream);
   }

@@ -413,6 +413,26 @@ cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cud
   return SB_LAUNCHED();
 }
 
+// result[m] = <e, y_m>, m = 0..2, over n entries (multi-block)        (sparse_mlpoly.rs:412-423 evaluate_with_tables)
+__global__ void __launch_bounds__(256) dot3_kernel(const fl_t* __restrict__ e, const fl_t* __restrict__ yA, const fl_t* __restrict__ yB,
+                                                   const fl_t* __restrict__ yC, size_t n, fl_t* partials, unsigned int* counter,
+                                                   fl_t* result) {
+  __shared__ fl_t smem[3 * 32];
+  fl_t acc[3];
+  acc[0] = acc[1] = acc[2] = fl_zero();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    fl_t x = ldg_fl(e + i);
+    acc[0] = fl_add(acc[0], fl_mul(x, ldg_fl(yA + i)));
+    acc[1] = fl_add(acc[1], fl_mul(x, ldg_fl(yB + i)));
+    acc[2] = fl_add(acc[2], fl_mul(x, ldg_fl(yC + i)));
+  }
+  grid_sum_fl<3>(acc, smem, partials, counter, result);
+}
+cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC, size_t n, const ScWork& w, cudaStream_t s) {
+  dot3_kernel<<<sc_grid(n, w), 256, 0, s>>>(e, yA, yB, yC, n, w.partials, w.counter, w.result);
+  return SB_LAUNCHED();
+}
+
 // ------------------------------------------------------------------ bullet reduction, scalar side
 // One block.  State: a, b (length n_cur, Montgomery), coeff (length R/n_cur) with
 //   G_k[i] = sum_t coeff[t] * G[t*n_cur + i]           (the folded generators, never materialised)
@@ -560,7 +580,7 @@ size_t msm_scratch_bytes(uint32_t rows, uint32_t n) {
 }
 cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, const fl_t* extra_h,
                       const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch, uint8_t* out32,
-                      cudaStream_t s) {
+                      cudaStream_t s, cudaEvent_t* ev) {
   (void)extra_q;
   (void)q_index;
   if (!rows) return cudaSuccess;
@@ -568,9 +588,11 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   uint32_t per = (n + p.splits - 1) / p.splits;
   int block = per >= 256 ? 256 : per >= 128 ? 128 : 64;
   dim3 grid(p.splits, rows);
+  if (ev) cudaEventRecord(ev[0], s);
   msm_fixed_kernel<<<grid, block, block * sizeof(ge_t), s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index,
                                                               reinterpret_cast<ge_t*>(scratch));
   cudaError_t e = SB_LAUNCHED();
+  if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
   msm_finish_kernel<<<(rows + 63) / 64, 64, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
   return SB_LAUNCHED();

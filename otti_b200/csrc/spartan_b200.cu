@@ -22,7 +22,8 @@ namespace sbh {
 static thread_local std::string g_err;
 void set_error(const std::string& s) { g_err = s; }
 const char* get_error() { return g_err.c_str(); }
-static thread_local double g_profile[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+static thread_local double g_profile[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+static thread_local uint64_t g_h2d_bytes = 0, g_d2h_bytes = 0;
 
 static bool g_device_ok = false;
 static int ensure_device() {
@@ -413,6 +414,7 @@ static int workspace_init(const Instance& inst, uint32_t R) {
   const size_t Nc = inst.num_cons, Nv = inst.num_vars;
   const size_t ell = ilog2(Nv), Ls = (size_t)1 << (ell / 2);
   SB_CUDA(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 4; i++) SB_CUDA(cudaEventCreate(&w.ev[i]));
   SB_CUDA(w.vars_canon.alloc(Nv));
   SB_CUDA(w.varsM.alloc(Nv));
   SB_CUDA(w.z.alloc(2 * Nv));
@@ -561,12 +563,14 @@ struct ProverCtx {
     scw.max_blocks = 148 * 4;
   }
   int fetch(const void* dev, size_t bytes, size_t pinned_off = PinnedLayout::kResult) {
+    g_d2h_bytes += bytes;
     SB_CUDA(cudaMemcpyAsync(w.pinned + pinned_off, dev, bytes, cudaMemcpyDeviceToHost, w.stream));
     SB_CUDA(cudaStreamSynchronize(w.stream));
     return SB200_OK;
   }
   int upload_scalars(const FlVec& v, sb::fl_t* dev) {
     if (v.empty()) return SB200_OK;
+    g_h2d_bytes += v.size() * 32;
     memcpy(w.pinned + PinnedLayout::kUpload, v.data(), v.size() * 32);
     SB_CUDA(cudaMemcpyAsync(dev, w.pinned + PinnedLayout::kUpload, v.size() * 32, cudaMemcpyHostToDevice, w.stream));
     SB_CUDA(cudaStreamSynchronize(w.stream));
@@ -643,6 +647,7 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
   Workspace& w = inst.ws;
   cudaStream_t st = w.stream;
   sb::launch_count_reset();
+  g_h2d_bytes = g_d2h_bytes = 0;
   double t_begin = now_s(), t_h2d = 0;
 
   Tape tape(tape_seed);
@@ -653,7 +658,13 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
   // ---- witness to HBM: canonical copy feeds the MSM digits, Montgomery copy everything else
   {
     double t0 = now_s();
-    SB_CUDA(cudaMemcpyAsync(w.vars_canon.p, vars32, n_vars * 32, cudaMemcpyHostToDevice, st));
+    if (vars32) {
+      g_h2d_bytes += n_vars * 32;
+      SB_CUDA(cudaMemcpyAsync(w.vars_canon.p, vars32, n_vars * 32, cudaMemcpyHostToDevice, st));
+    } else if (w.resident_vars != n_vars) {
+      set_error("vars32 == NULL but no witness of that length is resident (sb200_witness_upload)");
+      return SB200_ERR_ARG;
+    }
     if (Nv > n_vars) SB_CUDA(cudaMemsetAsync(w.vars_canon.p + n_vars, 0, (Nv - n_vars) * 32, st));  // Assignment::pad, lib.rs:92-105
     SB_CUDA(cudaMemsetAsync(w.flag.p, 0, 4, st));
     SB_CUDA(sb::k_to_mont(w.vars_canon.p, w.varsM.p, Nv, w.flag.p, st));
@@ -686,11 +697,12 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
       fl_to_bytes(blinds_vars[i], &bb[32 * i]);           // canonical, for the MSM
       memcpy(&bb[32 * (Ls + i)], blinds_vars[i].v, 32);   // Montgomery, for LZ_blind
     }
+    g_h2d_bytes += bb.size();
     SB_CUDA(cudaMemcpyAsync(w.blinds.p, bb.data(), bb.size(), cudaMemcpyHostToDevice, st));
     SB_CUDA(cudaStreamSynchronize(st));
   }
   SB_CUDA(sb::msm_fixed(gens.table, w.vars_canon.p, Rs, (uint32_t)Ls, (uint32_t)Rs, w.blinds.p, nullptr, (uint32_t)Rs, 0,
-                        w.msm_scratch.p, w.pts.p, st));
+                        w.msm_scratch.p, w.pts.p, st, w.ev));
   rc = ctx.fetch(w.pts.p, Ls * 32, PinnedLayout::kPoints);
   if (rc) return rc;
   pf.comm_vars.resize(Ls);
@@ -711,7 +723,9 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
   {
     size_t len = Nc;
     auto launch = [&](bool bind, const Fl& r) {
+      if (!bind) cudaEventRecord(w.ev[2], st);
       cudaError_t e = sb::k_sc_cubic(w.T.p, w.A.p, w.B.p, w.C.p, len, bind, to_dev(r), ctx.scw, st);
+      if (!bind) cudaEventRecord(w.ev[3], st);
       if (bind) len /= 2;
       return e;
     };
@@ -719,6 +733,7 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
     if (rc) return rc;
   }
   // final claims poly_tau[0], poly_Az[0], poly_Bz[0], poly_Cz[0]
+  g_d2h_bytes += 128 + 64 + 64;  // final claims of both phases, a[0]/b[0]
   SB_CUDA(cudaMemcpyAsync(w.pinned + 0, w.T.p, 32, cudaMemcpyDeviceToHost, st));
   SB_CUDA(cudaMemcpyAsync(w.pinned + 32, w.A.p, 32, cudaMemcpyDeviceToHost, st));
   SB_CUDA(cudaMemcpyAsync(w.pinned + 64, w.B.p, 32, cudaMemcpyDeviceToHost, st));
@@ -921,6 +936,13 @@ static int prove_impl(const Instance& inst, const uint8_t* vars32, uint64_t n_va
   g_profile[5] = t_h2d;
   g_profile[6] = ctx.host_fs;
   g_profile[7] = (double)sb::launch_count();
+  {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, w.ev[0], w.ev[1]) == cudaSuccess) g_profile[10] = ms * 1e-3;
+    if (cudaEventElapsedTime(&ms, w.ev[2], w.ev[3]) == cudaSuccess) g_profile[11] = ms * 1e-3;
+  }
+  g_profile[8] = (double)g_h2d_bytes;
+  g_profile[9] = (double)g_d2h_bytes;
   return SB200_OK;
 }
 
@@ -946,7 +968,7 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
                      uint64_t n_inputs, const sb200_gens* hg, const sb200_transcript_vt* transcript, const uint8_t* label,
                      size_t label_len, const uint8_t* tape_seed64, const sb200_comm_vt* comm, uint8_t** proof_out,
                      size_t* proof_len) {
-  if (!hi || !hg || !proof_out || !proof_len || (!vars32 && n_vars) || (!inputs32 && n_inputs)) return SB200_ERR_ARG;
+  if (!hi || !hg || !proof_out || !proof_len || (!inputs32 && n_inputs)) return SB200_ERR_ARG;
   if (comm && comm->world > 1) { set_error("sharded prove: use sb200_nizk_prove with world == 1 in this build"); return SB200_ERR_ARG; }
   int rc = ensure_device();
   if (rc) return rc;
@@ -981,11 +1003,33 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
   return SB200_OK;
 }
 
-int sb200_last_prove_profile(double out[8]) {
-  for (int i = 0; i < 8; i++) out[i] = g_profile[i];
+// Places the witness in HBM ahead of time; a following sb200_nizk_prove with vars32 == NULL and the same
+// n_vars uses it (the "inputs already resident" measurement of bench.py).
+int sb200_witness_upload(const sb200_instance* hi, const sb200_gens* hg, const uint8_t* vars32, uint64_t n_vars) {
+  if (!hi || !hg || (!vars32 && n_vars)) return SB200_ERR_ARG;
+  int rc = ensure_device();
+  if (rc) return rc;
+  const Instance& inst = *reinterpret_cast<const Instance*>(hi);
+  if (n_vars > inst.num_vars) return SB200_ERR_ARG;
+  rc = workspace_init(inst, reinterpret_cast<const Gens*>(hg)->R);
+  if (rc) return rc;
+  Workspace& w = inst.ws;
+  SB_CUDA(cudaMemcpyAsync(w.vars_canon.p, vars32, n_vars * 32, cudaMemcpyHostToDevice, w.stream));
+  SB_CUDA(cudaStreamSynchronize(w.stream));
+  w.resident_vars = n_vars;
+  return SB200_OK;
+}
+// cudaStream_t the instance's kernels run on (for CUDA-event timing by the caller); 0 before the first prove
+uint64_t sb200_instance_stream(const sb200_instance* hi) {
+  return hi ? (uint64_t)(uintptr_t) reinterpret_cast<const Instance*>(hi)->ws.stream : 0;
+}
+
+int sb200_last_prove_profile(double out[12]) {
+  for (int i = 0; i < 12; i++) out[i] = g_profile[i];
   return SB200_OK;
 }
 
 }  // extern "C"
 
+#include "verify.inc"
 #include "kernel_hooks.inc"

@@ -313,3 +313,73 @@ def test_transcript_state_advances_and_tape_randomness(sb):
     for p in (p1, pa, pb):
         assert O.nizk_verify(oi, oin, og, LABEL, p.to_bytes()) == 0
     assert p1.r1cs_sat_proof_len == len(p1.to_bytes()) - (8 + 32 * 6) - (8 + 32 * 7)
+
+
+@pytest.mark.parametrize("s", [1, 4, 6, 10])
+def test_nizk_verify_accepts_and_rejects(sb, s):
+    """NIZK::verify (lib.rs:538-574) on the device path: accepts the GPU proof AND the oracle's proof,
+    agrees with the oracle verifier on tampered proofs, wrong inputs, wrong label."""
+    n = 1 << s
+    ni = min(10, n - 1)
+    oi, ov, oin = O.Instance.synthetic(n, n, ni, 77)
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, ni, 77)
+    og, pg = O.Gens(n, n, ni), sb.NIZKGens.new(n, n, ni)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    oracle_proof = O.nizk_prove(oi, ov, oin, og, LABEL, bytes(64))  # different tape seed -> different valid proof
+    assert sb.NIZK(oracle_proof).verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    b = proof.to_bytes()
+    rng = random.Random(s)
+    for off in [40, len(b) - 1, len(b) // 2] + [rng.randrange(8, len(b)) for _ in range(12)]:
+        bad = bytearray(b)
+        bad[off] ^= 1 << rng.randrange(8)
+        want = O.nizk_verify(oi, oin, og, LABEL, bytes(bad))
+        if want == 0:
+            continue  # (a flipped bit inside a length prefix may still parse to the same proof -- never happens in practice)
+        with pytest.raises(sb.ProofVerifyError):
+            sb.NIZK(bytes(bad)).verify(pi, pin, sb.Transcript.new(LABEL), pg)
+    with pytest.raises(sb.ProofVerifyError):
+        proof.verify(pi, pin, sb.Transcript.new(b"other"), pg)
+    if ni:
+        wrong = canon([(int.from_bytes(oin[:32], "little") + 1) % ELL]) + oin[32:]
+        with pytest.raises(sb.ProofVerifyError):
+            proof.verify(pi, sb.InputsAssignment.new(wrong), sb.Transcript.new(LABEL), pg)
+    with pytest.raises(sb.ProofVerifyError):
+        sb.NIZK(b[:-1]).verify(pi, pin, sb.Transcript.new(LABEL), pg)
+
+
+def test_large_round_trip_properties(sb):
+    """BASELINE size (2^16, configs[1]) and 2^18: proof length equals the closed form (App. A.4), prove -> verify
+    round trip on the device, commitment rows are linear in the witness rows (homomorphism check on 2 rows)."""
+    for s in (16, 18):
+        n = 1 << s
+        pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, 10, 5)
+        pg = sb.NIZKGens.new(n, n, 10)
+        proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+        lL = s // 2
+        dpp = lambda k: 32 + 32 + 8 + 32 * k + 32 + 32
+        sc = lambda rounds, k: (8 + 32 * rounds) * 2 + 8 + rounds * dpp(k)
+        want_len = (8 + 32 * (1 << lL)) + sc(s, 4) + 128 + 352 + 64 + sc(s + 1, 3) + 32 + (2 * (8 + 32 * (s - lL)) + 128) + 64
+        assert proof.r1cs_sat_proof_len == want_len
+        assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    # 2^16 byte-identity against the oracle (the oracle needs ~2 s here)
+    oi, ov, oin = O.Instance.synthetic(1 << 16, 1 << 16, 10, 5)
+    og = O.Gens(1 << 16, 1 << 16, 10)
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(1 << 16, 1 << 16, 10, 5)
+    pg = sb.NIZKGens.new(1 << 16, 1 << 16, 10)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED, 8)
+    # Pedersen homomorphism: Com(x; r) + Com(y; s) == Com(x + y; r + s), row-wise on the device MSM
+    R = 256
+    xs, ys = rand_scalars(R, 1), rand_scalars(R, 2)
+    zs = [(a + b) % ELL for a, b in zip(xs, ys)]
+    bl = rand_scalars(2, 3)
+    o = _out(96)
+    Z = canon(xs + ys + zs + [0] * R)
+    blinds = canon([bl[0], bl[1], (bl[0] + bl[1]) % ELL, 0])
+    assert sb.lib().sb200_k_commit_rows(pg.h, _buf(Z), C.c_size_t(4 * R), _buf(blinds), C.c_size_t(4), _out(128)) == 0
+    out = _out(128)
+    sb.lib().sb200_k_commit_rows(pg.h, _buf(Z), C.c_size_t(4 * R), _buf(blinds), C.c_size_t(4), out)
+    out = bytes(out)
+    assert O.pt_add(out[:32], out[32:64]) == out[64:96]
+    assert out[96:] == bytes(32)  # the all-zero row commits to the identity
