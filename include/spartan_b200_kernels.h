@@ -19,6 +19,10 @@ extern "C" {
 
 /* Scalar add / sub / mul (op 0/1/2), elementwise over n                 ristretto255.rs:702-755 */
 int sb200_k_fl_binop(int op, const uint8_t* a, const uint8_t* b, uint8_t* out, size_t n);
+/* Coordinate field F_p, p = 2^255-19 (curve25519-dalek FieldElement behind group.rs:6-7): out = canonical
+ * bytes of a op b over n elements given as ANY 256-bit little-endian integers (op 0 add, 1 sub, 2 mul,
+ * 3 a^2, 4 a^-1) */
+int sb200_k_fp_binop(int op, const uint8_t* a, const uint8_t* b, uint8_t* out, size_t n);
 /* Scalar::from_bytes over n canonical values; *any_invalid = 1 if one is >= l   ristretto255.rs:398-422 */
 int sb200_k_to_mont(const uint8_t* canon, uint8_t* out, size_t n, int* any_invalid);
 /* Scalar::to_bytes over n values                                           ristretto255.rs:426-438 */

@@ -41,6 +41,9 @@ cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaS
 cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s);
 // out[i] = a[i] op b[i]  (op 0 add, 1 sub, 2 mul) -- parity-test hook for the limb arithmetic
 cudaError_t k_fl_binop(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n, cudaStream_t s);
+// F_p (2^255-19) parity-test hook: out[i] = canon(a[i] op b[i]), op 0 add, 1 sub, 2 mul, 3 sqr(a), 4 invert(a)
+struct fp_t;
+cudaError_t k_fp_binop(int op, const fp_t* a, const fp_t* b, fp_t* out, size_t n, cudaStream_t s);
 // flag[0] |= 1 unless A[i]*B[i] == C[i] for all i                     (r1csinstance.rs:238-245)
 cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, uint32_t* flag, cudaStream_t s);
 // eq(r) table of length 2^ell                                         (dense_mlpoly.rs:67-83)

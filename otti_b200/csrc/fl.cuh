@@ -11,6 +11,7 @@
 // the GPU.
 #pragma once
 #include <stdint.h>
+#include "mp.cuh"
 
 #ifdef __CUDACC__
 #define SB_HD __host__ __device__ __forceinline__
@@ -82,7 +83,7 @@ SB_HD fl_t fl_cond_sub_l(const fl_t& t) {
   for (int i = 0; i < 8; i++) r.v[i] = borrow ? t.v[i] : d.v[i];
   return r;
 }
-SB_HD fl_t fl_add(const fl_t& a, const fl_t& b) {
+SB_HD fl_t fl_add_portable(const fl_t& a, const fl_t& b) {
   fl_t t;
   uint64_t c = 0;
 #pragma unroll
@@ -93,7 +94,7 @@ SB_HD fl_t fl_add(const fl_t& a, const fl_t& b) {
   }
   return fl_cond_sub_l(t);
 }
-SB_HD fl_t fl_sub(const fl_t& a, const fl_t& b) {
+SB_HD fl_t fl_sub_portable(const fl_t& a, const fl_t& b) {
   fl_t d;
   uint64_t borrow = 0;
 #pragma unroll
@@ -112,12 +113,10 @@ SB_HD fl_t fl_sub(const fl_t& a, const fl_t& b) {
   }
   return d;
 }
-SB_HD fl_t fl_neg(const fl_t& a) { return fl_sub(fl_zero(), a); }
-SB_HD fl_t fl_dbl(const fl_t& a) { return fl_add(a, a); }
 
 // Montgomery product a*b*2^-256 mod l, CIOS over 32-bit words.  The zero limbs
 // of l (4..6) drop out of the reduction at compile time.
-SB_HD fl_t fl_mul(const fl_t& a, const fl_t& b) {
+SB_HD fl_t fl_mul_portable(const fl_t& a, const fl_t& b) {
   uint32_t t[10];
 #pragma unroll
   for (int i = 0; i < 10; i++) t[i] = 0;
@@ -153,6 +152,96 @@ SB_HD fl_t fl_mul(const fl_t& a, const fl_t& b) {
   for (int i = 0; i < 8; i++) r.v[i] = t[i];
   return fl_cond_sub_l(r);
 }
+#if defined(__CUDA_ARCH__)
+// ---- sm_100a versions: PTX carry chains (mp.cuh); bit-identical results to the portable code.
+__device__ __forceinline__ fl_t fl_cond_sub_l_dev(const uint32_t* t) {
+  uint32_t d0, d1, d2, d3, d4, d5, d6, d7, bw;
+  asm("sub.cc.u32 %0,%9,%17;\n\tsubc.cc.u32 %1,%10,%18;\n\tsubc.cc.u32 %2,%11,%19;\n\tsubc.cc.u32 %3,%12,%20;\n\t"
+      "subc.cc.u32 %4,%13,0;\n\tsubc.cc.u32 %5,%14,0;\n\tsubc.cc.u32 %6,%15,0;\n\tsubc.cc.u32 %7,%16,%21;\n\tsubc.u32 %8,0,0;"
+      : "=r"(d0), "=r"(d1), "=r"(d2), "=r"(d3), "=r"(d4), "=r"(d5), "=r"(d6), "=r"(d7), "=r"(bw)
+      : "r"(t[0]), "r"(t[1]), "r"(t[2]), "r"(t[3]), "r"(t[4]), "r"(t[5]), "r"(t[6]), "r"(t[7]),
+        "r"(SB_FL_L0), "r"(SB_FL_L1), "r"(SB_FL_L2), "r"(SB_FL_L3), "r"(SB_FL_L7));
+  fl_t r;
+  r.v[0] = bw ? t[0] : d0; r.v[1] = bw ? t[1] : d1; r.v[2] = bw ? t[2] : d2; r.v[3] = bw ? t[3] : d3;
+  r.v[4] = bw ? t[4] : d4; r.v[5] = bw ? t[5] : d5; r.v[6] = bw ? t[6] : d6; r.v[7] = bw ? t[7] : d7;
+  return r;
+}
+__device__ __forceinline__ fl_t fl_add(const fl_t& a, const fl_t& b) {
+  uint32_t t[8];
+  asm("add.cc.u32 %0,%8,%16;\n\taddc.cc.u32 %1,%9,%17;\n\taddc.cc.u32 %2,%10,%18;\n\taddc.cc.u32 %3,%11,%19;\n\t"
+      "addc.cc.u32 %4,%12,%20;\n\taddc.cc.u32 %5,%13,%21;\n\taddc.cc.u32 %6,%14,%22;\n\taddc.u32 %7,%15,%23;"
+      : "=r"(t[0]), "=r"(t[1]), "=r"(t[2]), "=r"(t[3]), "=r"(t[4]), "=r"(t[5]), "=r"(t[6]), "=r"(t[7])
+      : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+        "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+  return fl_cond_sub_l_dev(t);
+}
+__device__ __forceinline__ fl_t fl_sub(const fl_t& a, const fl_t& b) {
+  fl_t d;
+  uint32_t bw;
+  asm("sub.cc.u32 %0,%9,%17;\n\tsubc.cc.u32 %1,%10,%18;\n\tsubc.cc.u32 %2,%11,%19;\n\tsubc.cc.u32 %3,%12,%20;\n\t"
+      "subc.cc.u32 %4,%13,%21;\n\tsubc.cc.u32 %5,%14,%22;\n\tsubc.cc.u32 %6,%15,%23;\n\tsubc.cc.u32 %7,%16,%24;\n\tsubc.u32 %8,0,0;"
+      : "=r"(d.v[0]), "=r"(d.v[1]), "=r"(d.v[2]), "=r"(d.v[3]), "=r"(d.v[4]), "=r"(d.v[5]), "=r"(d.v[6]), "=r"(d.v[7]), "=r"(bw)
+      : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+        "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+  asm("add.cc.u32 %0,%0,%8;\n\taddc.cc.u32 %1,%1,%9;\n\taddc.cc.u32 %2,%2,%10;\n\taddc.cc.u32 %3,%3,%11;\n\t"
+      "addc.cc.u32 %4,%4,0;\n\taddc.cc.u32 %5,%5,0;\n\taddc.cc.u32 %6,%6,0;\n\taddc.u32 %7,%7,%12;"
+      : "+r"(d.v[0]), "+r"(d.v[1]), "+r"(d.v[2]), "+r"(d.v[3]), "+r"(d.v[4]), "+r"(d.v[5]), "+r"(d.v[6]), "+r"(d.v[7])
+      : "r"(bw & SB_FL_L0), "r"(bw & SB_FL_L1), "r"(bw & SB_FL_L2), "r"(bw & SB_FL_L3), "r"(bw & SB_FL_L7));
+  return d;
+}
+// Montgomery product a*b*2^-256 mod l.  Full 16-limb product (mp_mul8), then word-by-word
+// reduction t += m_i * l * 2^(32 i) with m_i = t_i * (-l^-1) mod 2^32, split by the shape
+// of l = L0 + L1 2^32 + L2 2^64 + L3 2^96 + 2^252:
+//   * the L0 product and the running carry stay in one 64-bit chain (it makes limb i zero);
+//   * the L1, L3 products (limbs i+1.., i+3..) and the L2 product (limbs i+2..) are
+//     accumulated lazily in two parity-split accumulators Ev / Od, whose integer values
+//     never exceed (m_0..m_i) * 2^125 -- hence no carry out of limb i+4;
+//   * the 2^252 term is a 4-bit shift of (m_7..m_0), added once at the end; only m_0's low
+//     nibble reaches limb 7 and so feeds m_7.
+__device__ __forceinline__ fl_t fl_mul(const fl_t& a, const fl_t& b) {
+  uint32_t t[16];
+  mp_mul8(t, a.v, b.v);
+  uint32_t acc[2][12];  // acc[p][k]: limb k of the accumulator for positions of parity p
+#pragma unroll
+  for (int k = 0; k < 12; k++) acc[0][k] = acc[1][k] = 0;
+  uint32_t m[9];
+  m[8] = 0;
+  uint64_t carry = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    uint64_t cur = carry + t[i] + acc[0][i] + acc[1][i];
+    if (i == 7) cur += (uint64_t)(m[0] << 28);
+    m[i] = (uint32_t)cur * SB_FL_INV32;
+    cur += (uint64_t)m[i] * SB_FL_L0;
+    carry = cur >> 32;
+    uint32_t* X = acc[(i + 1) & 1];
+    uint32_t* Y = acc[i & 1];
+    asm("mad.lo.cc.u32 %0,%4,%5,%0;\n\tmadc.hi.cc.u32 %1,%4,%5,%1;\n\tmadc.lo.cc.u32 %2,%4,%6,%2;\n\tmadc.hi.u32 %3,%4,%6,%3;"
+        : "+r"(X[i + 1]), "+r"(X[i + 2]), "+r"(X[i + 3]), "+r"(X[i + 4])
+        : "r"(m[i]), "r"(SB_FL_L1), "r"(SB_FL_L3));
+    asm("mad.lo.cc.u32 %0,%3,%4,%0;\n\tmadc.hi.cc.u32 %1,%3,%4,%1;\n\taddc.u32 %2,%2,0;"
+        : "+r"(Y[i + 2]), "+r"(Y[i + 3]), "+r"(Y[i + 4])
+        : "r"(m[i]), "r"(SB_FL_L2));
+  }
+  // r = t_hi + Ev_hi + Od_hi + ((m_7..m_0) >> 4) + carry   (< 2l)
+  uint32_t r[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    uint32_t msh = (m[k] >> 4) | (m[k + 1] << 28);
+    carry += (uint64_t)t[8 + k] + msh;
+    if (k < 4) carry += (uint64_t)acc[0][8 + k] + acc[1][8 + k];
+    r[k] = (uint32_t)carry;
+    carry >>= 32;
+  }
+  return fl_cond_sub_l_dev(r);
+}
+#else
+SB_HD fl_t fl_add(const fl_t& a, const fl_t& b) { return fl_add_portable(a, b); }
+SB_HD fl_t fl_sub(const fl_t& a, const fl_t& b) { return fl_sub_portable(a, b); }
+SB_HD fl_t fl_mul(const fl_t& a, const fl_t& b) { return fl_mul_portable(a, b); }
+#endif
+SB_HD fl_t fl_neg(const fl_t& a) { return fl_sub(fl_zero(), a); }
+SB_HD fl_t fl_dbl(const fl_t& a) { return fl_add(a, a); }
 SB_HD fl_t fl_sqr(const fl_t& a) { return fl_mul(a, a); }
 
 // canonical integer (< l) -> Montgomery: Scalar::from_bytes multiplies by R2 (ristretto255.rs:417-419)

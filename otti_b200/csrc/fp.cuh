@@ -9,6 +9,7 @@
 // Plain C, __host__ __device__: the limb logic is unit-tested on the CPU.
 #pragma once
 #include "fl.cuh"
+#include "mp.cuh"
 
 namespace sb {
 
@@ -57,7 +58,7 @@ SB_HD fp_t fp_fold_small(const fp_t& x, uint32_t k38) {
   }
   return r;
 }
-SB_HD fp_t fp_add(const fp_t& a, const fp_t& b) {
+SB_HD fp_t fp_add_portable(const fp_t& a, const fp_t& b) {
   fp_t t;
   uint64_t c = 0;
 #pragma unroll
@@ -68,7 +69,7 @@ SB_HD fp_t fp_add(const fp_t& a, const fp_t& b) {
   }
   return fp_fold_small(t, (uint32_t)c * 38u);
 }
-SB_HD fp_t fp_sub(const fp_t& a, const fp_t& b) {
+SB_HD fp_t fp_sub_portable(const fp_t& a, const fp_t& b) {
   fp_t d;
   uint64_t borrow = 0;
 #pragma unroll
@@ -97,7 +98,6 @@ SB_HD fp_t fp_sub(const fp_t& a, const fp_t& b) {
   }
   return r;
 }
-SB_HD fp_t fp_neg(const fp_t& a) { return fp_sub(fp_zero(), a); }
 
 // 16-limb product folded to 8 limbs: lo + 38*hi
 SB_HD fp_t fp_reduce16(const uint32_t t[16]) {
@@ -114,7 +114,7 @@ SB_HD fp_t fp_reduce16(const uint32_t t[16]) {
   for (int i = 0; i < 8; i++) x.v[i] = r[i];
   return fp_fold_small(x, (uint32_t)c * 38u);  // c < 39 -> c*38 < 2^11
 }
-SB_HD fp_t fp_mul(const fp_t& a, const fp_t& b) {
+SB_HD fp_t fp_mul_portable(const fp_t& a, const fp_t& b) {
   uint32_t t[16];
 #pragma unroll
   for (int i = 0; i < 16; i++) t[i] = 0;
@@ -131,7 +131,74 @@ SB_HD fp_t fp_mul(const fp_t& a, const fp_t& b) {
   }
   return fp_reduce16(t);
 }
-SB_HD fp_t fp_sqr(const fp_t& a) { return fp_mul(a, a); }
+SB_HD fp_t fp_sqr_portable(const fp_t& a) { return fp_mul_portable(a, a); }
+#if defined(__CUDA_ARCH__)
+// ---- sm_100a versions: PTX carry chains (mp.cuh).  Same loose-form contract as the portable code.
+__device__ __forceinline__ fp_t fp_add(const fp_t& a, const fp_t& b) {
+  fp_t r;
+  uint32_t c;
+  asm("add.cc.u32 %0,%9,%17;\n\taddc.cc.u32 %1,%10,%18;\n\taddc.cc.u32 %2,%11,%19;\n\taddc.cc.u32 %3,%12,%20;\n\t"
+      "addc.cc.u32 %4,%13,%21;\n\taddc.cc.u32 %5,%14,%22;\n\taddc.cc.u32 %6,%15,%23;\n\taddc.cc.u32 %7,%16,%24;\n\taddc.u32 %8,0,0;"
+      : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]), "=r"(c)
+      : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+        "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+  // 2^256 = 38: fold the carry; a second wrap leaves a value < 38, so the last +38 touches limb 0 only
+  asm("mad.lo.cc.u32 %0,%8,38,%0;\n\taddc.cc.u32 %1,%1,0;\n\taddc.cc.u32 %2,%2,0;\n\taddc.cc.u32 %3,%3,0;\n\t"
+      "addc.cc.u32 %4,%4,0;\n\taddc.cc.u32 %5,%5,0;\n\taddc.cc.u32 %6,%6,0;\n\taddc.cc.u32 %7,%7,0;\n\taddc.u32 %8,0,0;\n\t"
+      "mad.lo.u32 %0,%8,38,%0;"
+      : "+r"(r.v[0]), "+r"(r.v[1]), "+r"(r.v[2]), "+r"(r.v[3]), "+r"(r.v[4]), "+r"(r.v[5]), "+r"(r.v[6]), "+r"(r.v[7]), "+r"(c));
+  return r;
+}
+__device__ __forceinline__ fp_t fp_sub(const fp_t& a, const fp_t& b) {
+  fp_t r;
+  uint32_t bw;
+  asm("sub.cc.u32 %0,%9,%17;\n\tsubc.cc.u32 %1,%10,%18;\n\tsubc.cc.u32 %2,%11,%19;\n\tsubc.cc.u32 %3,%12,%20;\n\t"
+      "subc.cc.u32 %4,%13,%21;\n\tsubc.cc.u32 %5,%14,%22;\n\tsubc.cc.u32 %6,%15,%23;\n\tsubc.cc.u32 %7,%16,%24;\n\tsubc.u32 %8,0,0;"
+      : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]), "=r"(r.v[6]), "=r"(r.v[7]), "=r"(bw)
+      : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+        "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+  // wrapped by 2^256 = 38 (mod p): take 38 off again; a second wrap leaves >= 2^256 - 38, so the last -38 touches limb 0 only
+  uint32_t k = bw & 38u;
+  asm("sub.cc.u32 %0,%0,%8;\n\tsubc.cc.u32 %1,%1,0;\n\tsubc.cc.u32 %2,%2,0;\n\tsubc.cc.u32 %3,%3,0;\n\t"
+      "subc.cc.u32 %4,%4,0;\n\tsubc.cc.u32 %5,%5,0;\n\tsubc.cc.u32 %6,%6,0;\n\tsubc.cc.u32 %7,%7,0;\n\tsubc.u32 %8,0,0;"
+      : "+r"(r.v[0]), "+r"(r.v[1]), "+r"(r.v[2]), "+r"(r.v[3]), "+r"(r.v[4]), "+r"(r.v[5]), "+r"(r.v[6]), "+r"(r.v[7]), "+r"(k));
+  r.v[0] -= k & 38u;
+  return r;
+}
+// t[0..16) -> lo + 38 * hi, folded into 8 limbs
+__device__ __forceinline__ fp_t fp_reduce16_dev(const uint32_t* t) {
+  uint32_t r0, r1, r2, r3, r4, r5, r6, r7, r8;
+  asm("mad.lo.cc.u32 %0,%9,38,%13;\n\tmadc.hi.cc.u32 %1,%9,38,%14;\n\tmadc.lo.cc.u32 %2,%10,38,%15;\n\tmadc.hi.cc.u32 %3,%10,38,%16;\n\t"
+      "madc.lo.cc.u32 %4,%11,38,%17;\n\tmadc.hi.cc.u32 %5,%11,38,%18;\n\tmadc.lo.cc.u32 %6,%12,38,%19;\n\tmadc.hi.cc.u32 %7,%12,38,%20;\n\t"
+      "addc.u32 %8,0,0;"
+      : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7), "=r"(r8)
+      : "r"(t[8]), "r"(t[10]), "r"(t[12]), "r"(t[14]), "r"(t[0]), "r"(t[1]), "r"(t[2]), "r"(t[3]), "r"(t[4]), "r"(t[5]), "r"(t[6]), "r"(t[7]));
+  asm("mad.lo.cc.u32 %0,%8,38,%0;\n\tmadc.hi.cc.u32 %1,%8,38,%1;\n\tmadc.lo.cc.u32 %2,%9,38,%2;\n\tmadc.hi.cc.u32 %3,%9,38,%3;\n\t"
+      "madc.lo.cc.u32 %4,%10,38,%4;\n\tmadc.hi.cc.u32 %5,%10,38,%5;\n\tmadc.lo.cc.u32 %6,%11,38,%6;\n\tmadc.hi.u32 %7,%11,38,%7;"
+      : "+r"(r1), "+r"(r2), "+r"(r3), "+r"(r4), "+r"(r5), "+r"(r6), "+r"(r7), "+r"(r8)
+      : "r"(t[9]), "r"(t[11]), "r"(t[13]), "r"(t[15]));
+  // r8 < 39 + 1: fold it (r8 * 38 < 2^11); a second wrap leaves a tiny value, so the last +38 touches limb 0 only
+  asm("mad.lo.cc.u32 %0,%8,38,%0;\n\taddc.cc.u32 %1,%1,0;\n\taddc.cc.u32 %2,%2,0;\n\taddc.cc.u32 %3,%3,0;\n\t"
+      "addc.cc.u32 %4,%4,0;\n\taddc.cc.u32 %5,%5,0;\n\taddc.cc.u32 %6,%6,0;\n\taddc.cc.u32 %7,%7,0;\n\taddc.u32 %8,0,0;\n\t"
+      "mad.lo.u32 %0,%8,38,%0;"
+      : "+r"(r0), "+r"(r1), "+r"(r2), "+r"(r3), "+r"(r4), "+r"(r5), "+r"(r6), "+r"(r7), "+r"(r8));
+  fp_t x;
+  x.v[0] = r0; x.v[1] = r1; x.v[2] = r2; x.v[3] = r3; x.v[4] = r4; x.v[5] = r5; x.v[6] = r6; x.v[7] = r7;
+  return x;
+}
+__device__ __forceinline__ fp_t fp_mul(const fp_t& a, const fp_t& b) {
+  uint32_t t[16];
+  mp_mul8(t, a.v, b.v);
+  return fp_reduce16_dev(t);
+}
+__device__ __forceinline__ fp_t fp_sqr(const fp_t& a) { return fp_mul(a, a); }
+#else
+SB_HD fp_t fp_add(const fp_t& a, const fp_t& b) { return fp_add_portable(a, b); }
+SB_HD fp_t fp_sub(const fp_t& a, const fp_t& b) { return fp_sub_portable(a, b); }
+SB_HD fp_t fp_mul(const fp_t& a, const fp_t& b) { return fp_mul_portable(a, b); }
+SB_HD fp_t fp_sqr(const fp_t& a) { return fp_mul_portable(a, a); }
+#endif
+SB_HD fp_t fp_neg(const fp_t& a) { return fp_sub(fp_zero(), a); }
 SB_HD fp_t fp_mul_small(const fp_t& a, uint32_t k) {  // k < 2^26
   fp_t x;
   uint64_t c = 0;

@@ -156,6 +156,19 @@ static inline unsigned grid_for(size_t n, int block, int per_sm = 8) {
   size_t cap = (size_t)kSMs * per_sm;
   return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
 }
+__global__ void fp_binop_kernel(int op, const fp_t* a, const fp_t* b, fp_t* out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    fp_t x = ldg_fp(a + i), y = ldg_fp(b + i);
+    fp_t r = op == 0 ? fp_add(x, y) : op == 1 ? fp_sub(x, y) : op == 2 ? fp_mul(x, y) : op == 3 ? fp_sqr(x) : fp_invert(x);
+    st_fp(out + i, fp_canon(r));
+  }
+}
+cudaError_t k_fp_binop(int op, const fp_t* a, const fp_t* b, fp_t* out, size_t n, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  fp_binop_kernel<<<grid_for(n, 128), 128, 0, s>>>(op, a, b, out, n);
+  return SB_LAUNCHED();
+}
 cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s) {
   if (!n) return cudaSuccess;
   to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n, flag);

@@ -49,6 +49,32 @@ def test_fl_binops(sb):
         assert got == mont([f(x, y) for x, y in zip(xs, ys)])
 
 
+def test_fp_binops(sb):
+    """Coordinate field 2^255-19 on the device (PTX carry chains) == Python integers, on loose 256-bit inputs."""
+    import random
+    P = 2**255 - 19
+    rnd = random.Random(5)
+    edge = [0, 1, 2, 18, 19, 37, 38, 39, P - 1, P, P + 1, 2 * P, 2 * P + 37, 2**256 - 1, 2**256 - 38, 2**256 - 39, 2**255,
+            2**255 - 1, 2**224, 2**32 - 1, 2**64 - 1, (2**256 - 1) ^ (2**128 - 1), 2**128 - 1]
+    n = 4096
+    xs = edge + [rnd.getrandbits(256) for _ in range(n - len(edge))]
+    ys = list(reversed(edge)) + [rnd.getrandbits(256) for _ in range(n - len(edge))]
+    for i in range(len(edge)):  # every edge pair at least once
+        for j in range(len(edge)):
+            xs.append(edge[i]); ys.append(edge[j])
+    n = len(xs)
+    a = b"".join(x.to_bytes(32, "little") for x in xs)
+    b = b"".join(y.to_bytes(32, "little") for y in ys)
+    ops = {0: lambda x, y: (x + y) % P, 1: lambda x, y: (x - y) % P, 2: lambda x, y: x * y % P, 3: lambda x, y: x * x % P,
+           4: lambda x, y: pow(x % P, P - 2, P)}
+    for op, f in ops.items():
+        o = _out(32 * n)
+        assert sb.lib().sb200_k_fp_binop(op, _buf(a), _buf(b), o, C.c_size_t(n)) == 0
+        got = bytes(o)
+        for i, (x, y) in enumerate(zip(xs, ys)):
+            assert int.from_bytes(got[32 * i:32 * i + 32], "little") == f(x, y), (op, i, hex(x), hex(y))
+
+
 def test_to_from_mont_and_canonicity(sb):
     """Scalar::from_bytes / to_bytes (ristretto255.rs:398-438) incl. rejection of values >= l."""
     xs = EDGE + rand_scalars(1000, 3)
