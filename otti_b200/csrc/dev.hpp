@@ -34,6 +34,16 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
                       const fl_t* extra_h, const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch,
                       uint8_t* out32, cudaStream_t s, cudaEvent_t* ev = nullptr);  // ev[0..1] bracket the main kernel
 size_t msm_scratch_bytes(uint32_t rows, uint32_t n);
+// Latency-oriented variant for a few rows (bullet reduction, one-row commitments): every (term, window)
+// pair is a unit of work, the sum is left UNCOMPRESSED in out_ext[rows] (extended coordinates X,Y,Z,T as
+// 4 x 8 LE words each, any representative < 2^256).  counters: rows + 1 zeroed words, self-resetting.
+// If host_flag != NULL, out_ext may be mapped host memory and *host_flag = seq is written after all rows.
+cudaError_t msm_small(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, void* scratch,
+                      unsigned int* counters, void* out_ext, uint32_t* host_flag, uint32_t seq, cudaStream_t s);
+size_t msm_small_scratch_bytes(uint32_t rows, uint32_t n, uint32_t windows);
+// first element of up to four device vectors -> host mailbox (mapped memory), then *host_flag = seq
+cudaError_t k_mail(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
+                   uint32_t seq, cudaStream_t s);
 
 // ---- F_l vector kernels -------------------------------------------------------------------
 // canonical -> Montgomery, flag[0] |= 1 if any input >= l            (lib.rs:65-89)
@@ -67,6 +77,12 @@ struct ScWork {
   unsigned int* counter;
   fl_t* result;        // device [3]
   uint32_t max_blocks;
+  // optional mailbox in mapped pinned host memory: the last block also stores the three sums there,
+  // fences (system scope) and then writes `seq` to host_flag, so the host can spin on the flag
+  // instead of paying a copy + stream synchronise per Fiat-Shamir round
+  fl_t* host_result = nullptr;
+  uint32_t* host_flag = nullptr;
+  uint32_t seq = 0;
 };
 // One fused round of the cubic ZK sum-check (sumcheck.rs:618-674):
 //  if do_bind: tables (length n_old) are bound at r in place -> length n_old/2   (dense_mlpoly.rs:214-221)

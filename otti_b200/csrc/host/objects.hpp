@@ -70,11 +70,15 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   DevBuf<uint8_t> msm_scratch, pts;
   uint8_t* pinned = nullptr;  // host staging
   size_t pinned_bytes = 0;
+  uint8_t* mail = nullptr;      // mapped pinned mailbox the kernels write round results + flags into (prover.inc Mail)
+  uint8_t* mail_dev = nullptr;  // the same memory as seen from the device
+  uint32_t seq = 0;             // mailbox sequence number, never reused
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // [0,1] commit MSM kernel, [2,3] first cubic round
   ~Workspace() {
     for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);
     if (pinned) cudaFreeHost(pinned);
+    if (mail) cudaFreeHost(mail);
     if (stream) cudaStreamDestroy(stream);
   }
 };

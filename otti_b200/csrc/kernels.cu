@@ -100,8 +100,14 @@ __device__ __forceinline__ void block_sum_fl(fl_t (&x)[NV], fl_t* smem) {
 }
 // Grid-wide sum by "last block done": every block deposits NV partials, the last one to
 // arrive adds them up (F_l addition is exact, so arrival order cannot change a bit).
+struct Mailbox {  // see ScWork
+  fl_t* host_result;
+  uint32_t* host_flag;
+  uint32_t seq;
+};
 template <int NV>
-__device__ __forceinline__ void grid_sum_fl(fl_t (&x)[NV], fl_t* smem, fl_t* partials, unsigned int* counter, fl_t* result) {
+__device__ __forceinline__ void grid_sum_fl(fl_t (&x)[NV], fl_t* smem, fl_t* partials, unsigned int* counter, fl_t* result,
+                                            Mailbox mb = Mailbox{nullptr, nullptr, 0}) {
   __shared__ bool s_last;
   block_sum_fl<NV>(x, smem);
   if (threadIdx.x == 0) {
@@ -125,6 +131,12 @@ __device__ __forceinline__ void grid_sum_fl(fl_t (&x)[NV], fl_t* smem, fl_t* par
 #pragma unroll
       for (int k = 0; k < NV; k++) st_fl(&result[k], acc[k]);
       *counter = 0;
+      if (mb.host_flag != nullptr) {
+#pragma unroll
+        for (int k = 0; k < NV; k++) st_fl(&mb.host_result[k], acc[k]);
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(mb.host_flag) = mb.seq;
+      }
     }
   }
 }
@@ -288,7 +300,7 @@ __device__ __forceinline__ fl_t bind1(const fl_t& lo, const fl_t& hi, const fl_t
 template <bool BIND>
 __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
                                                        fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
-                                                       unsigned int* counter, fl_t* result) {
+                                                       unsigned int* counter, fl_t* result, Mailbox mb) {
   __shared__ fl_t smem[3 * 32];
   const size_t h = newlen >> 1;
   fl_t e[3];
@@ -326,11 +338,11 @@ __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_
 #pragma unroll
     for (int k = 0; k < 4; k++) st_fl(tabs[k], bind1(ld_fl(tabs[k]), ld_fl(tabs[k] + 1), r));
   }
-  grid_sum_fl<3>(e, smem, partials, counter, result);
+  grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
 template <bool BIND>
 __global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
-                                                      fl_t* partials, unsigned int* counter, fl_t* result) {
+                                                      fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
   __shared__ fl_t smem[3 * 32];
   const size_t h = newlen >> 1;
   fl_t e[3];
@@ -354,7 +366,7 @@ __global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t
     st_fl(Z, bind1(ld_fl(Z), ld_fl(Z + 1), r));
     st_fl(Q, bind1(ld_fl(Q), ld_fl(Q + 1), r));
   }
-  grid_sum_fl<3>(e, smem, partials, counter, result);
+  grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
 static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
   size_t g = (pairs + 255) / 256;
@@ -366,15 +378,17 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
                        cudaStream_t s) {
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
-  if (do_bind) sc_cubic_kernel<true><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result);
-  else sc_cubic_kernel<false><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result);
+  Mailbox mb{w.host_result, w.host_flag, w.seq};
+  if (do_bind) sc_cubic_kernel<true><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  else sc_cubic_kernel<false><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
   return SB_LAUNCHED();
 }
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s) {
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
-  if (do_bind) sc_quad_kernel<true><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result);
-  else sc_quad_kernel<false><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result);
+  Mailbox mb{w.host_result, w.host_flag, w.seq};
+  if (do_bind) sc_quad_kernel<true><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  else sc_quad_kernel<false><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
   return SB_LAUNCHED();
 }
 
@@ -608,6 +622,146 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
   msm_finish_kernel<<<(rows + 63) / 64, 64, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
+  return SB_LAUNCHED();
+}
+
+// ------------------------------------------------------------------ small fixed-base MSM (latency path)
+// The bullet reduction and the one-row commitments of the evaluation proof are a handful of MSMs
+// of R+2 terms on the critical path of a Fiat-Shamir round: what matters is latency, not
+// throughput.  Here every (term, window) pair is its own unit of work -- a thread does one or two
+// table look-ups -- and the points are summed by a shuffle tree, a shared-memory tree and a
+// last-block-done tree.  The result is left in EXTENDED coordinates (optionally in mapped host
+// memory, followed by a flag): one point compression is ~280 dependent field multiplications,
+// which a host core does in ~4 us and a lone GPU thread in ~40 us.
+__device__ __forceinline__ ge_t warp_sum_ge(ge_t x) {
+#pragma unroll 1
+  for (int o = 16; o > 0; o >>= 1) {
+    ge_t y;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      y.X.v[i] = __shfl_down_sync(0xffffffffu, x.X.v[i], o);
+      y.Y.v[i] = __shfl_down_sync(0xffffffffu, x.Y.v[i], o);
+      y.Z.v[i] = __shfl_down_sync(0xffffffffu, x.Z.v[i], o);
+      y.T.v[i] = __shfl_down_sync(0xffffffffu, x.T.v[i], o);
+    }
+    x = ge_add(x, y);
+  }
+  return x;
+}
+// valid in thread 0; smem: ge_t[blockDim.x / 32]
+__device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  x = warp_sum_ge(x);
+  __syncthreads();
+  if (lane == 0) smem[wid] = x;
+  __syncthreads();
+  if (wid == 0) {
+    x = lane < nw ? smem[lane] : ge_identity();
+    x = warp_sum_ge(x);
+  }
+  return x;
+}
+// digit `w` of the signed radix-2^c recoding of the scalar at kp (carry recomputed from the lower windows)
+__device__ __forceinline__ int32_t msm_digit_at(const uint32_t* kp, uint32_t w, uint32_t c) {
+  uint32_t carry = 0;
+  int32_t d = 0;
+  for (uint32_t i = 0; i <= w; i++) d = msm_digit(kp, i, c, carry);
+  return d;
+}
+__global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
+                                                        const fl_t* __restrict__ scalars, size_t stride, uint32_t n,
+                                                        ge_t* partial, unsigned int* counters, ge_t* out,
+                                                        uint32_t* host_flag, uint32_t seq) {
+  __shared__ ge_t smem[8];
+  __shared__ bool s_last;
+  const uint32_t row = blockIdx.y, rows = gridDim.y;
+  const size_t epb = (size_t)windows << (c - 1);
+  const uint32_t pairs = n * windows;
+  ge_t acc = ge_identity();
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < pairs; p += gridDim.x * blockDim.x) {
+    uint32_t j = p / windows, w = p - j * windows;
+    uint32_t k[8];
+    const uint4* q = reinterpret_cast<const uint4*>(scalars + (size_t)row * stride + j);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    k[0] = a.x; k[1] = a.y; k[2] = a.z; k[3] = a.w; k[4] = b.x; k[5] = b.y; k[6] = b.z; k[7] = b.w;
+    if ((k[0] | k[1] | k[2] | k[3] | k[4] | k[5] | k[6] | k[7]) == 0) continue;
+    int32_t d = msm_digit_at(k, w, c);
+    if (d != 0) {
+      bool neg = d < 0;
+      uint32_t mag = (uint32_t)(neg ? -d : d);
+      niels_t e = ldg_niels(tbl + (size_t)j * epb + ((size_t)w << (c - 1)) + (mag - 1));
+      acc = ge_madd(acc, e, neg);
+    }
+  }
+  acc = block_sum_ge(acc, smem);
+  if (threadIdx.x == 0) {
+    partial[(size_t)row * gridDim.x + blockIdx.x] = acc;
+    __threadfence();
+    unsigned int t = atomicAdd(&counters[row], 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  acc = ge_identity();
+  for (uint32_t b = threadIdx.x; b < gridDim.x; b += blockDim.x) {
+    const uint4* src = reinterpret_cast<const uint4*>(&partial[(size_t)row * gridDim.x + b]);
+    ge_t tmp;
+    uint32_t* tw = reinterpret_cast<uint32_t*>(&tmp);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      uint4 v = __ldcg(src + i);
+      tw[4 * i] = v.x; tw[4 * i + 1] = v.y; tw[4 * i + 2] = v.z; tw[4 * i + 3] = v.w;
+    }
+    acc = ge_add(acc, tmp);
+  }
+  acc = block_sum_ge(acc, smem);
+  if (threadIdx.x == 0) {
+    out[row] = acc;
+    counters[row] = 0;
+    if (host_flag != nullptr) {
+      __threadfence_system();
+      unsigned int t = atomicAdd(&counters[rows], 1u);  // rows finished
+      if (t == rows - 1) {
+        counters[rows] = 0;
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(host_flag) = seq;
+      }
+    }
+  }
+}
+uint32_t msm_small_blocks(uint32_t rows, uint32_t n, uint32_t windows) {
+  uint32_t pairs = n * windows;
+  uint32_t want = (pairs + 511) / 512;  // ~2 look-ups per thread
+  uint32_t cap = (uint32_t)(kSMs * 2) / (rows ? rows : 1);
+  if (cap < 1) cap = 1;
+  if (want < 1) want = 1;
+  return want < cap ? want : cap;
+}
+size_t msm_small_scratch_bytes(uint32_t rows, uint32_t n, uint32_t windows) {
+  return (size_t)rows * msm_small_blocks(rows, n, windows) * sizeof(ge_t);
+}
+cudaError_t msm_small(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, void* scratch,
+                      unsigned int* counters, void* out_ext, uint32_t* host_flag, uint32_t seq, cudaStream_t s) {
+  if (!rows) return cudaSuccess;
+  dim3 grid(msm_small_blocks(rows, n, t.windows), rows);
+  msm_small_kernel<<<grid, 256, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, reinterpret_cast<ge_t*>(scratch), counters,
+                                        reinterpret_cast<ge_t*>(out_ext), host_flag, seq);
+  return SB_LAUNCHED();
+}
+// up to four scalars (the first element of each source) to a host mailbox, then the flag
+__global__ void mail_kernel(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
+                            uint32_t seq) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const fl_t* src[4] = {p0, p1, p2, p3};
+    for (int i = 0; i < n; i++) st_fl(host + i, ld_fl(src[i]));
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t*>(host_flag) = seq;
+  }
+}
+cudaError_t k_mail(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
+                   uint32_t seq, cudaStream_t s) {
+  mail_kernel<<<1, 32, 0, s>>>(p0, p1, p2, p3, n, host, host_flag, seq);
   return SB_LAUNCHED();
 }
 
