@@ -243,6 +243,16 @@ SB_HD fl_t fl_mul(const fl_t& a, const fl_t& b) { return fl_mul_portable(a, b); 
 SB_HD fl_t fl_neg(const fl_t& a) { return fl_sub(fl_zero(), a); }
 SB_HD fl_t fl_dbl(const fl_t& a) { return fl_add(a, a); }
 SB_HD fl_t fl_sqr(const fl_t& a) { return fl_mul(a, a); }
+// multiplication policies, see FpInl / FpCall in fp.cuh
+struct FlInl {
+  static SB_HD fl_t mul(const fl_t& a, const fl_t& b) { return fl_mul(a, b); }
+};
+#if defined(__CUDACC__)
+static __device__ __noinline__ fl_t fl_mul_call(fl_t a, fl_t b) { return fl_mul(a, b); }
+struct FlCall {
+  static __device__ __forceinline__ fl_t mul(const fl_t& a, const fl_t& b) { return fl_mul_call(a, b); }
+};
+#endif
 
 // canonical integer (< l) -> Montgomery: Scalar::from_bytes multiplies by R2 (ristretto255.rs:417-419)
 SB_HD fl_t fl_to_mont(const fl_t& canon) { return fl_mul(canon, fl_r2()); }

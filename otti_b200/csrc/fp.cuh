@@ -256,28 +256,50 @@ SB_HD bool fp_eq(const fp_t& a, const fp_t& b) { return fp_is_zero(fp_sub(a, b))
 SB_HD bool fp_is_neg(const fp_t& a) { return fp_canon(a).v[0] & 1u; }
 SB_HD fp_t fp_abs(const fp_t& a) { return fp_is_neg(a) ? fp_neg(a) : a; }
 
-SB_HD fp_t fp_pow2k(fp_t a, int k) {
-  for (int i = 0; i < k; i++) a = fp_sqr(a);
+// Field-operation policies: Inl expands every multiplication in place (throughput kernels, the
+// loop body is reused); Call goes through one out-of-line copy per kernel, which keeps the code of
+// the latency-bound kernels (one pass over a long dependent chain) inside the instruction cache.
+struct FpInl {
+  static SB_HD fp_t mul(const fp_t& a, const fp_t& b) { return fp_mul(a, b); }
+  static SB_HD fp_t sqr(const fp_t& a) { return fp_sqr(a); }
+};
+#if defined(__CUDACC__)
+static __device__ __noinline__ fp_t fp_mul_call(fp_t a, fp_t b) { return fp_mul(a, b); }
+struct FpCall {
+  static __device__ __forceinline__ fp_t mul(const fp_t& a, const fp_t& b) { return fp_mul_call(a, b); }
+  static __device__ __forceinline__ fp_t sqr(const fp_t& a) { return fp_mul_call(a, a); }
+};
+#endif
+
+template <class F>
+SB_HD fp_t fp_pow2k_t(fp_t a, int k) {
+#pragma unroll 1
+  for (int i = 0; i < k; i++) a = F::sqr(a);
   return a;
 }
 // a^((p-5)/8) = a^(2^252 - 3)
-SB_HD fp_t fp_pow_p58(const fp_t& z) {
-  fp_t z2 = fp_sqr(z), z9 = fp_mul(fp_pow2k(z2, 2), z), z11 = fp_mul(z9, z2);
-  fp_t z2_5_0 = fp_mul(fp_sqr(z11), z9);
-  fp_t z2_10_0 = fp_mul(fp_pow2k(z2_5_0, 5), z2_5_0);
-  fp_t z2_20_0 = fp_mul(fp_pow2k(z2_10_0, 10), z2_10_0);
-  fp_t z2_40_0 = fp_mul(fp_pow2k(z2_20_0, 20), z2_20_0);
-  fp_t z2_50_0 = fp_mul(fp_pow2k(z2_40_0, 10), z2_10_0);
-  fp_t z2_100_0 = fp_mul(fp_pow2k(z2_50_0, 50), z2_50_0);
-  fp_t z2_200_0 = fp_mul(fp_pow2k(z2_100_0, 100), z2_100_0);
-  fp_t z2_250_0 = fp_mul(fp_pow2k(z2_200_0, 50), z2_50_0);
-  return fp_mul(fp_pow2k(z2_250_0, 2), z);
+template <class F>
+SB_HD fp_t fp_pow_p58_t(const fp_t& z) {
+  fp_t z2 = F::sqr(z), z9 = F::mul(fp_pow2k_t<F>(z2, 2), z), z11 = F::mul(z9, z2);
+  fp_t z2_5_0 = F::mul(F::sqr(z11), z9);
+  fp_t z2_10_0 = F::mul(fp_pow2k_t<F>(z2_5_0, 5), z2_5_0);
+  fp_t z2_20_0 = F::mul(fp_pow2k_t<F>(z2_10_0, 10), z2_10_0);
+  fp_t z2_40_0 = F::mul(fp_pow2k_t<F>(z2_20_0, 20), z2_20_0);
+  fp_t z2_50_0 = F::mul(fp_pow2k_t<F>(z2_40_0, 10), z2_10_0);
+  fp_t z2_100_0 = F::mul(fp_pow2k_t<F>(z2_50_0, 50), z2_50_0);
+  fp_t z2_200_0 = F::mul(fp_pow2k_t<F>(z2_100_0, 100), z2_100_0);
+  fp_t z2_250_0 = F::mul(fp_pow2k_t<F>(z2_200_0, 50), z2_50_0);
+  return F::mul(fp_pow2k_t<F>(z2_250_0, 2), z);
 }
 // a^(p-2)
-SB_HD fp_t fp_invert(const fp_t& z) {
+template <class F>
+SB_HD fp_t fp_invert_t(const fp_t& z) {
   // a^(2^255-21) = (a^(2^252-3))^8 * a^3
-  fp_t t = fp_pow2k(fp_pow_p58(z), 3);
-  return fp_mul(t, fp_mul(fp_sqr(z), z));
+  fp_t t = fp_pow2k_t<F>(fp_pow_p58_t<F>(z), 3);
+  return F::mul(t, F::mul(F::sqr(z), z));
 }
+SB_HD fp_t fp_pow2k(fp_t a, int k) { return fp_pow2k_t<FpInl>(a, k); }
+SB_HD fp_t fp_pow_p58(const fp_t& z) { return fp_pow_p58_t<FpInl>(z); }
+SB_HD fp_t fp_invert(const fp_t& z) { return fp_invert_t<FpInl>(z); }
 
 }  // namespace sb

@@ -28,43 +28,55 @@ SB_HD niels_t niels_identity() {
   return n;
 }
 // full addition, 9M (add-2008-hwcd-3 with k = 2d)
-SB_HD ge_t ge_add(const ge_t& p, const ge_t& q) {
-  fp_t A = fp_mul(fp_sub(p.Y, p.X), fp_sub(q.Y, q.X));
-  fp_t B = fp_mul(fp_add(p.Y, p.X), fp_add(q.Y, q.X));
-  fp_t C = fp_mul(fp_mul(p.T, q.T), fp_2d());
-  fp_t D = fp_mul(p.Z, q.Z);
+template <class F>
+SB_HD ge_t ge_add_t(const ge_t& p, const ge_t& q) {
+  fp_t A = F::mul(fp_sub(p.Y, p.X), fp_sub(q.Y, q.X));
+  fp_t B = F::mul(fp_add(p.Y, p.X), fp_add(q.Y, q.X));
+  fp_t C = F::mul(F::mul(p.T, q.T), fp_2d());
+  fp_t D = F::mul(p.Z, q.Z);
   D = fp_add(D, D);
-  fp_t E = fp_sub(B, A), F = fp_sub(D, C), G = fp_add(D, C), H = fp_add(B, A);
+  fp_t E = fp_sub(B, A), Fv = fp_sub(D, C), G = fp_add(D, C), H = fp_add(B, A);
   ge_t r;
-  r.X = fp_mul(E, F); r.Y = fp_mul(G, H); r.Z = fp_mul(F, G); r.T = fp_mul(E, H);
+  r.X = F::mul(E, Fv); r.Y = F::mul(G, H); r.Z = F::mul(Fv, G); r.T = F::mul(E, H);
   return r;
 }
 // mixed addition with an affine Niels entry, 7M; sign = true adds the negation
-SB_HD ge_t ge_madd(const ge_t& p, const niels_t& q, bool neg) {
+template <class F>
+SB_HD ge_t ge_madd_t(const ge_t& p, const niels_t& q, bool neg) {
   fp_t ypx = fp_add(p.Y, p.X), ymx = fp_sub(p.Y, p.X);
-  fp_t A = fp_mul(ymx, neg ? q.yplusx : q.yminusx);
-  fp_t B = fp_mul(ypx, neg ? q.yminusx : q.yplusx);
-  fp_t C = fp_mul(p.T, q.xy2d);
+  fp_t A = F::mul(ymx, neg ? q.yplusx : q.yminusx);
+  fp_t B = F::mul(ypx, neg ? q.yminusx : q.yplusx);
+  fp_t C = F::mul(p.T, q.xy2d);
   fp_t D = fp_add(p.Z, p.Z);
   fp_t E = fp_sub(B, A), H = fp_add(B, A);
-  fp_t F = neg ? fp_add(D, C) : fp_sub(D, C);
+  fp_t Fv = neg ? fp_add(D, C) : fp_sub(D, C);
   fp_t G = neg ? fp_sub(D, C) : fp_add(D, C);
   ge_t r;
-  r.X = fp_mul(E, F); r.Y = fp_mul(G, H); r.Z = fp_mul(F, G); r.T = fp_mul(E, H);
+  r.X = F::mul(E, Fv); r.Y = F::mul(G, H); r.Z = F::mul(Fv, G); r.T = F::mul(E, H);
   return r;
 }
 // doubling (dbl-2008-hwcd, a = -1), 4S + 4M
-SB_HD ge_t ge_double(const ge_t& p) {
-  fp_t A = fp_sqr(p.X), B = fp_sqr(p.Y), C = fp_sqr(p.Z);
+template <class F>
+SB_HD ge_t ge_double_t(const ge_t& p) {
+  fp_t A = F::sqr(p.X), B = F::sqr(p.Y), C = F::sqr(p.Z);
   C = fp_add(C, C);
   fp_t D = fp_neg(A);
   fp_t xy = fp_add(p.X, p.Y);
-  fp_t E = fp_sub(fp_sub(fp_sqr(xy), A), B);
-  fp_t G = fp_add(D, B), F = fp_sub(G, C), H = fp_sub(D, B);
+  fp_t E = fp_sub(fp_sub(F::sqr(xy), A), B);
+  fp_t G = fp_add(D, B), Fv = fp_sub(G, C), H = fp_sub(D, B);
   ge_t r;
-  r.X = fp_mul(E, F); r.Y = fp_mul(G, H); r.Z = fp_mul(F, G); r.T = fp_mul(E, H);
+  r.X = F::mul(E, Fv); r.Y = F::mul(G, H); r.Z = F::mul(Fv, G); r.T = F::mul(E, H);
   return r;
 }
+SB_HD ge_t ge_add(const ge_t& p, const ge_t& q) { return ge_add_t<FpInl>(p, q); }
+SB_HD ge_t ge_madd(const ge_t& p, const niels_t& q, bool neg) { return ge_madd_t<FpInl>(p, q, neg); }
+SB_HD ge_t ge_double(const ge_t& p) { return ge_double_t<FpInl>(p); }
+#if defined(__CUDACC__)
+// one out-of-line copy per kernel (see FpCall): for the tree reductions and table builds
+static __device__ __noinline__ ge_t ge_add_call(ge_t p, ge_t q) { return ge_add_t<FpInl>(p, q); }
+static __device__ __noinline__ ge_t ge_madd_call(ge_t p, niels_t q, bool neg) { return ge_madd_t<FpInl>(p, q, neg); }
+static __device__ __noinline__ ge_t ge_double_call(ge_t p) { return ge_double_t<FpInl>(p); }
+#endif
 // affine (x, y) -> Niels
 SB_HD niels_t niels_from_affine(const fp_t& x, const fp_t& y) {
   niels_t n;
@@ -79,35 +91,39 @@ SB_HD fp_t fp_invsqrt_a_minus_d() { return fp_set(0x805d40eau, 0x99c8fdaau, 0x5a
 
 // SQRT_RATIO_M1(1, v): returns abs(r) with r^2 * v in {1, -1, -sqrt(-1)...}; only the
 // "inverse square root" value is needed by compress.
-SB_HD fp_t fp_invsqrt(const fp_t& v) {
-  fp_t v3 = fp_mul(fp_sqr(v), v), v7 = fp_mul(fp_sqr(v3), v);
-  fp_t r = fp_mul(v3, fp_pow_p58(v7));
-  fp_t c = fp_mul(v, fp_sqr(r));
+template <class F>
+SB_HD fp_t fp_invsqrt_t(const fp_t& v) {
+  fp_t v3 = F::mul(F::sqr(v), v), v7 = F::mul(F::sqr(v3), v);
+  fp_t r = F::mul(v3, fp_pow_p58_t<F>(v7));
+  fp_t c = F::mul(v, F::sqr(r));
   fp_t one = fp_one(), m1 = fp_neg(one);
   bool f = fp_eq(c, m1), fi = fp_eq(c, fp_neg(fp_sqrt_m1()));
-  if (f || fi) r = fp_mul(r, fp_sqrt_m1());
+  if (f || fi) r = F::mul(r, fp_sqrt_m1());
   return fp_abs(r);
 }
 // RistrettoPoint::compress -> canonical 32 bytes (8 LE words)
-SB_HD void ge_compress(const ge_t& p, uint32_t out[8]) {
-  fp_t u1 = fp_mul(fp_add(p.Z, p.Y), fp_sub(p.Z, p.Y));
-  fp_t u2 = fp_mul(p.X, p.Y);
-  fp_t inv = fp_invsqrt(fp_mul(u1, fp_sqr(u2)));
-  fp_t d1 = fp_mul(inv, u1), d2 = fp_mul(inv, u2);
-  fp_t zinv = fp_mul(fp_mul(d1, d2), p.T);
+template <class F>
+SB_HD void ge_compress_t(const ge_t& p, uint32_t out[8]) {
+  fp_t u1 = F::mul(fp_add(p.Z, p.Y), fp_sub(p.Z, p.Y));
+  fp_t u2 = F::mul(p.X, p.Y);
+  fp_t inv = fp_invsqrt_t<F>(F::mul(u1, F::sqr(u2)));
+  fp_t d1 = F::mul(inv, u1), d2 = F::mul(inv, u2);
+  fp_t zinv = F::mul(F::mul(d1, d2), p.T);
   fp_t x, y, dn;
-  if (fp_is_neg(fp_mul(p.T, zinv))) {
-    x = fp_mul(p.Y, fp_sqrt_m1());
-    y = fp_mul(p.X, fp_sqrt_m1());
-    dn = fp_mul(d1, fp_invsqrt_a_minus_d());
+  if (fp_is_neg(F::mul(p.T, zinv))) {
+    x = F::mul(p.Y, fp_sqrt_m1());
+    y = F::mul(p.X, fp_sqrt_m1());
+    dn = F::mul(d1, fp_invsqrt_a_minus_d());
   } else {
     x = p.X; y = p.Y; dn = d2;
   }
-  if (fp_is_neg(fp_mul(x, zinv))) y = fp_neg(y);
-  fp_t s = fp_canon(fp_abs(fp_mul(dn, fp_sub(p.Z, y))));
+  if (fp_is_neg(F::mul(x, zinv))) y = fp_neg(y);
+  fp_t s = fp_canon(fp_abs(F::mul(dn, fp_sub(p.Z, y))));
 #pragma unroll
   for (int i = 0; i < 8; i++) out[i] = s.v[i];
 }
+SB_HD fp_t fp_invsqrt(const fp_t& v) { return fp_invsqrt_t<FpInl>(v); }
+SB_HD void ge_compress(const ge_t& p, uint32_t out[8]) { ge_compress_t<FpInl>(p, out); }
 
 // Signed radix-2^c recoding used by the fixed-base MSM: digit w of the canonical scalar at kp
 // (8 LE words), in (-2^(c-1), 2^(c-1)], with the running carry.  floor(252/c)+1 windows cover

@@ -69,7 +69,7 @@ __device__ __forceinline__ void st_fp(fp_t* p, const fp_t& x) {
 
 // ------------------------------------------------------------------ reductions over F_l
 __device__ __forceinline__ fl_t warp_sum_fl(fl_t x) {
-#pragma unroll
+#pragma unroll 1
   for (int o = 16; o > 0; o >>= 1) {
     fl_t y;
 #pragma unroll
@@ -294,10 +294,13 @@ cudaError_t k_spmvT3_combine(const Csr& csc, uint32_t num_cols, const fl_t* e, f
 }
 
 // ------------------------------------------------------------------ sum-check rounds
+template <class M>
 __device__ __forceinline__ fl_t bind1(const fl_t& lo, const fl_t& hi, const fl_t& r) {
-  return fl_add(lo, fl_mul(r, fl_sub(hi, lo)));  // Z[i] + r*(Z[i+n] - Z[i]), dense_mlpoly.rs:217
+  return fl_add(lo, M::mul(r, fl_sub(hi, lo)));  // Z[i] + r*(Z[i+n] - Z[i]), dense_mlpoly.rs:217
 }
-template <bool BIND>
+// M = FlInl for the long rounds (the loop body is reused), FlCall for the short ones, where a round is
+// one pass over ~14 multiplications per thread and the kernel must stay inside the instruction cache.
+template <bool BIND, class M>
 __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
                                                        fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
                                                        unsigned int* counter, fl_t* result, Mailbox mb) {
@@ -312,8 +315,8 @@ __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_
     for (int k = 0; k < 4; k++) {
       fl_t* X = tabs[k];
       if (BIND) {
-        lo[k] = bind1(ld_fl(X + i), ld_fl(X + i + newlen), r);
-        hi[k] = bind1(ld_fl(X + i + h), ld_fl(X + i + h + newlen), r);
+        lo[k] = bind1<M>(ld_fl(X + i), ld_fl(X + i + newlen), r);
+        hi[k] = bind1<M>(ld_fl(X + i + h), ld_fl(X + i + h + newlen), r);
         st_fl(X + i, lo[k]);
         st_fl(X + i + h, hi[k]);
       } else {
@@ -322,25 +325,25 @@ __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_
       }
     }
     // comb(T,A,B,C) = T*(A*B - C) at the points 0, 2, 3 (sumcheck.rs:622-650, r1csproof.rs:84-88)
-    e[0] = fl_add(e[0], fl_mul(lo[0], fl_sub(fl_mul(lo[1], lo[2]), lo[3])));
+    e[0] = fl_add(e[0], M::mul(lo[0], fl_sub(M::mul(lo[1], lo[2]), lo[3])));
     fl_t d[4], p[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
       d[k] = fl_sub(hi[k], lo[k]);
       p[k] = fl_add(hi[k], d[k]);  // 2*hi - lo
     }
-    e[1] = fl_add(e[1], fl_mul(p[0], fl_sub(fl_mul(p[1], p[2]), p[3])));
+    e[1] = fl_add(e[1], M::mul(p[0], fl_sub(M::mul(p[1], p[2]), p[3])));
 #pragma unroll
     for (int k = 0; k < 4; k++) p[k] = fl_add(p[k], d[k]);  // 3*hi - 2*lo
-    e[2] = fl_add(e[2], fl_mul(p[0], fl_sub(fl_mul(p[1], p[2]), p[3])));
+    e[2] = fl_add(e[2], M::mul(p[0], fl_sub(M::mul(p[1], p[2]), p[3])));
   }
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
 #pragma unroll
-    for (int k = 0; k < 4; k++) st_fl(tabs[k], bind1(ld_fl(tabs[k]), ld_fl(tabs[k] + 1), r));
+    for (int k = 0; k < 4; k++) st_fl(tabs[k], bind1<M>(ld_fl(tabs[k]), ld_fl(tabs[k] + 1), r));
   }
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
-template <bool BIND>
+template <bool BIND, class M>
 __global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
                                                       fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
   __shared__ fl_t smem[3 * 32];
@@ -350,24 +353,25 @@ __global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < h; i += (size_t)gridDim.x * blockDim.x) {
     fl_t zl, zh, ql, qh;
     if (BIND) {
-      zl = bind1(ld_fl(Z + i), ld_fl(Z + i + newlen), r);
-      zh = bind1(ld_fl(Z + i + h), ld_fl(Z + i + h + newlen), r);
-      ql = bind1(ld_fl(Q + i), ld_fl(Q + i + newlen), r);
-      qh = bind1(ld_fl(Q + i + h), ld_fl(Q + i + h + newlen), r);
+      zl = bind1<M>(ld_fl(Z + i), ld_fl(Z + i + newlen), r);
+      zh = bind1<M>(ld_fl(Z + i + h), ld_fl(Z + i + h + newlen), r);
+      ql = bind1<M>(ld_fl(Q + i), ld_fl(Q + i + newlen), r);
+      qh = bind1<M>(ld_fl(Q + i + h), ld_fl(Q + i + h + newlen), r);
       st_fl(Z + i, zl); st_fl(Z + i + h, zh); st_fl(Q + i, ql); st_fl(Q + i + h, qh);
     } else {
       zl = ld_fl(Z + i); zh = ld_fl(Z + i + h); ql = ld_fl(Q + i); qh = ld_fl(Q + i + h);
     }
-    e[0] = fl_add(e[0], fl_mul(zl, ql));  // sumcheck.rs:459-467
+    e[0] = fl_add(e[0], M::mul(zl, ql));  // sumcheck.rs:459-467
     fl_t z2 = fl_sub(fl_add(zh, zh), zl), q2 = fl_sub(fl_add(qh, qh), ql);
-    e[1] = fl_add(e[1], fl_mul(z2, q2));
+    e[1] = fl_add(e[1], M::mul(z2, q2));
   }
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x == 0) {
-    st_fl(Z, bind1(ld_fl(Z), ld_fl(Z + 1), r));
-    st_fl(Q, bind1(ld_fl(Q), ld_fl(Q + 1), r));
+    st_fl(Z, bind1<M>(ld_fl(Z), ld_fl(Z + 1), r));
+    st_fl(Q, bind1<M>(ld_fl(Q), ld_fl(Q + 1), r));
   }
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
+static constexpr unsigned kCompactBlocks = 148;  // rounds with at most one block per SM run the compact kernels
 static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
   size_t g = (pairs + 255) / 256;
   size_t cap = (size_t)kSMs * 4;
@@ -379,16 +383,22 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
-  if (do_bind) sc_cubic_kernel<true><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
-  else sc_cubic_kernel<false><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  const bool compact = g <= kCompactBlocks;
+  if (do_bind && compact) sc_cubic_kernel<true, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  else if (do_bind) sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  else if (compact) sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  else sc_cubic_kernel<false, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
   return SB_LAUNCHED();
 }
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s) {
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
-  if (do_bind) sc_quad_kernel<true><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
-  else sc_quad_kernel<false><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  const bool compact = g <= kCompactBlocks;
+  if (do_bind && compact) sc_quad_kernel<true, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  else if (do_bind) sc_quad_kernel<true, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  else if (compact) sc_quad_kernel<false, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  else sc_quad_kernel<false, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
   return SB_LAUNCHED();
 }
 
@@ -467,6 +477,11 @@ cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC
 //        (2) if n > 1: c_L = <a_L,b_R>, c_R = <a_R,b_L> and the two MSM scalar rows over the ORIGINAL
 //            bases:  L = sum a_L[i]*G_R[i] + c_L*Q + blind_L*H,  R = sum a_R[i]*G_L[i] + c_R*Q + blind_R*H
 //            (bullet.rs:79-96).  Rows have stride R+2: [0,R) bases G, [R] = H, [R+1] = Q; canonical form.
+__device__ __forceinline__ fl_t fl_from_mont_c(const fl_t& m) {
+  fl_t one = fl_zero();
+  one.v[0] = 1;
+  return fl_mul_call(m, one);
+}
 __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, const fl_t* coeff_in, fl_t* coeff_out,
                                                            uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv,
                                                            fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR) {
@@ -477,13 +492,13 @@ __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, con
     n = n_cur / 2;
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
       fl_t al = ld_fl(a + i), ar = ld_fl(a + n + i), bl = ld_fl(b + i), br = ld_fl(b + n + i);
-      st_fl(a + i, fl_add(fl_mul(al, u), fl_mul(u_inv, ar)));
-      st_fl(b + i, fl_add(fl_mul(bl, u_inv), fl_mul(u, br)));
+      st_fl(a + i, fl_add(FlCall::mul(al, u), FlCall::mul(u_inv, ar)));
+      st_fl(b + i, fl_add(FlCall::mul(bl, u_inv), FlCall::mul(u, br)));
     }
     for (uint32_t t = threadIdx.x; t < nco_in; t += blockDim.x) {
       fl_t c = ld_fl(coeff_in + t);
-      st_fl(coeff_out + 2 * t, fl_mul(c, u_inv));
-      st_fl(coeff_out + 2 * t + 1, fl_mul(c, u));
+      st_fl(coeff_out + 2 * t, FlCall::mul(c, u_inv));
+      st_fl(coeff_out + 2 * t + 1, FlCall::mul(c, u));
     }
     __syncthreads();
   }
@@ -494,8 +509,8 @@ __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, con
   c[0] = c[1] = fl_zero();
   for (uint32_t i = threadIdx.x; i < half; i += blockDim.x) {
     fl_t al = ld_fl(a + i), ar = ld_fl(a + half + i), bl = ld_fl(b + i), br = ld_fl(b + half + i);
-    c[0] = fl_add(c[0], fl_mul(al, br));
-    c[1] = fl_add(c[1], fl_mul(ar, bl));
+    c[0] = fl_add(c[0], FlCall::mul(al, br));
+    c[1] = fl_add(c[1], FlCall::mul(ar, bl));
   }
   block_sum_fl<2>(c, smem);
   const size_t stride = (size_t)Rsize + 2;
@@ -504,18 +519,18 @@ __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, con
     uint32_t t = g / n, pos = g % n;
     fl_t co = ld_fl(coeff + t);
     if (pos >= half) {
-      st_fl(sL + g, fl_from_mont(fl_mul(ld_fl(a + (pos - half)), co)));
+      st_fl(sL + g, fl_from_mont_c(FlCall::mul(ld_fl(a + (pos - half)), co)));
       st_fl(sR + g, fl_zero());
     } else {
-      st_fl(sR + g, fl_from_mont(fl_mul(ld_fl(a + half + pos), co)));
+      st_fl(sR + g, fl_from_mont_c(FlCall::mul(ld_fl(a + half + pos), co)));
       st_fl(sL + g, fl_zero());
     }
   }
   if (threadIdx.x == 0) {
-    st_fl(sL + Rsize, fl_from_mont(blind_L));
-    st_fl(sL + Rsize + 1, fl_from_mont(c[0]));
-    st_fl(sR + Rsize, fl_from_mont(blind_R));
-    st_fl(sR + Rsize + 1, fl_from_mont(c[1]));
+    st_fl(sL + Rsize, fl_from_mont_c(blind_L));
+    st_fl(sL + Rsize + 1, fl_from_mont_c(c[0]));
+    st_fl(sR + Rsize, fl_from_mont_c(blind_R));
+    st_fl(sR + Rsize + 1, fl_from_mont_c(c[1]));
   }
 }
 cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize, bool do_fold,
@@ -573,7 +588,7 @@ __global__ void __launch_bounds__(256) msm_fixed_kernel(const niels_t* __restric
   sm[threadIdx.x] = acc;
   __syncthreads();
   for (uint32_t o = blockDim.x >> 1; o > 0; o >>= 1) {
-    if (threadIdx.x < o) sm[threadIdx.x] = ge_add(sm[threadIdx.x], sm[threadIdx.x + o]);
+    if (threadIdx.x < o) sm[threadIdx.x] = ge_add_call(sm[threadIdx.x], sm[threadIdx.x + o]);
     __syncthreads();
   }
   if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = sm[0];
@@ -582,9 +597,9 @@ __global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t row
   uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= rows) return;
   ge_t acc = partial[(size_t)row * nsplit];
-  for (uint32_t s = 1; s < nsplit; s++) acc = ge_add(acc, partial[(size_t)row * nsplit + s]);
+  for (uint32_t s = 1; s < nsplit; s++) acc = ge_add_call(acc, partial[(size_t)row * nsplit + s]);
   uint32_t w[8];
-  ge_compress(acc, w);
+  ge_compress_t<FpCall>(acc, w);
   uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
   o[0] = make_uint4(w[0], w[1], w[2], w[3]);
   o[1] = make_uint4(w[4], w[5], w[6], w[7]);
@@ -621,7 +636,7 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
-  msm_finish_kernel<<<(rows + 63) / 64, 64, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
+  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
   return SB_LAUNCHED();
 }
 
@@ -644,7 +659,7 @@ __device__ __forceinline__ ge_t warp_sum_ge(ge_t x) {
       y.Z.v[i] = __shfl_down_sync(0xffffffffu, x.Z.v[i], o);
       y.T.v[i] = __shfl_down_sync(0xffffffffu, x.T.v[i], o);
     }
-    x = ge_add(x, y);
+    x = ge_add_call(x, y);
   }
   return x;
 }
@@ -690,7 +705,7 @@ __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restric
       bool neg = d < 0;
       uint32_t mag = (uint32_t)(neg ? -d : d);
       niels_t e = ldg_niels(tbl + (size_t)j * epb + ((size_t)w << (c - 1)) + (mag - 1));
-      acc = ge_madd(acc, e, neg);
+      acc = ge_madd_call(acc, e, neg);
     }
   }
   acc = block_sum_ge(acc, smem);
@@ -713,7 +728,7 @@ __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restric
       uint4 v = __ldcg(src + i);
       tw[4 * i] = v.x; tw[4 * i + 1] = v.y; tw[4 * i + 2] = v.z; tw[4 * i + 3] = v.w;
     }
-    acc = ge_add(acc, tmp);
+    acc = ge_add_call(acc, tmp);
   }
   acc = block_sum_ge(acc, smem);
   if (threadIdx.x == 0) {
@@ -783,32 +798,32 @@ __global__ void __launch_bounds__(64) msm_table_kernel(const fp_t* __restrict__ 
   P.X = ldg_fp(affine_xy + 2 * (size_t)base);
   P.Y = ldg_fp(affine_xy + 2 * (size_t)base + 1);
   P.Z = fp_one();
-  P.T = fp_mul(P.X, P.Y);
-  for (uint32_t k = 0; k < c * w; k++) P = ge_double(P);
+  P.T = fp_mul_call(P.X, P.Y);
+  for (uint32_t k = 0; k < c * w; k++) P = ge_double_call(P);
   // M = (chunk*ch + 1) * P
   uint32_t m0 = chunk * ch + 1;
   ge_t M = ge_identity();
   for (int bit = 15; bit >= 0; bit--) {
-    M = ge_double(M);
-    if ((m0 >> bit) & 1u) M = ge_add(M, P);
+    M = ge_double_call(M);
+    if ((m0 >> bit) & 1u) M = ge_add_call(M, P);
   }
   niels_t* slot = tbl + ((size_t)base * windows + w) * epw + (size_t)chunk * ch;
   fp_t pre[kTblChunk];
   fp_t acc = fp_one();
   for (uint32_t k = 0; k < ch; k++) {
     pre[k] = acc;
-    acc = fp_mul(acc, M.Z);
+    acc = fp_mul_call(acc, M.Z);
     st_fp(&slot[k].yplusx, M.X);
     st_fp(&slot[k].yminusx, M.Y);
     st_fp(&slot[k].xy2d, M.Z);
-    M = ge_add(M, P);
+    M = ge_add_call(M, P);
   }
-  fp_t inv = fp_invert(acc);
+  fp_t inv = fp_invert_t<FpCall>(acc);
   for (int k = (int)ch - 1; k >= 0; k--) {
     fp_t X = slot[k].yplusx, Y = slot[k].yminusx, Z = slot[k].xy2d;
-    fp_t zi = fp_mul(inv, pre[k]);
-    inv = fp_mul(inv, Z);
-    niels_t e = niels_from_affine(fp_mul(X, zi), fp_mul(Y, zi));
+    fp_t zi = fp_mul_call(inv, pre[k]);
+    inv = fp_mul_call(inv, Z);
+    niels_t e = niels_from_affine(fp_mul_call(X, zi), fp_mul_call(Y, zi));
     st_fp(&slot[k].yplusx, e.yplusx);
     st_fp(&slot[k].yminusx, e.yminusx);
     st_fp(&slot[k].xy2d, e.xy2d);
