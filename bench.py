@@ -216,26 +216,33 @@ def main():
     value = world * n * args.steps / (res_ms * 1e-3)
     e2e_value = world * n * args.steps / (e2e_ms * 1e-3)
 
-    # ---- roofline of the dominant kernel (commitment MSM), from CUDA events inside the timed region
+    # ---- roofline of the dominant kernel (commitment MSM), from CUDA events inside the timed region.
+    # The kernel is bound by the integer-multiply pipe (fmaheavy), not by HBM (DESIGN.md "Rooflines"):
+    #   algorithmic work  = terms x windows x (1 - 2^-c) mixed additions x 7 F_p multiplications x 75 IMAD.WIDE.U32
+    #   algorithmic bytes = one 32-byte scalar per term + one 96-byte table entry per mixed addition
     ell = s
     Ls, Rs = 1 << (ell // 2), 1 << (ell - ell // 2)
-    c = int(os.environ.get("SB200_MSM_WINDOW", "8"))
+    c = int(sb.lib().sb200_k_gens_window(gens.h))
     W = 252 // c + 1
     terms = n + Ls
+    madds = terms * W * (1 - 2.0 ** -c)
     k_s = prof["msm_commit_kernel"]
-    alg_bytes = terms * 32 + terms * W * (1 - 2.0 ** -c) * 96  # scalars + one 96-byte table entry per non-zero digit
+    alg_bytes = terms * 32 + madds * 96
     hbm_peak, which = measured_peaks()
     achieved = alg_bytes / k_s / 1e9 if k_s > 0 else 0.0
-    mul32 = terms * W * 7 * 64  # 7 F_p multiplications of 8x8 limbs per mixed add
+    imad = madds * 7 * 75  # IMAD.WIDE.U32 per F_p product: 64 partial products + 8 (x38 fold) + 3 (cuobjdump, fp.cuh)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    int_peak = 148 * 64 * sm_mhz * 1e6  # IMAD lanes/clk/SM (B300_MICROARCH.md:85) at the sampled SM clock
+    # fmaheavy issues one IMAD.WIDE.U32 warp instruction per 4 cycles per SM sub-partition (measured:
+    # profiles/r01_msm_fixed_2p20_v3.txt, 22.6 % inst rate at 80.8 % pipe-active) -> 8 lanes/clk/SMSP
+    int_peak = 148 * 4 * 8 * sm_mhz * 1e6
     roofline = {
-        "kernel": "msm_fixed_kernel (commitment rows, %d x %d)" % (Ls, Rs), "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
-        "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": which,
+        "kernel": "msm_fixed_kernel (commitment rows, %d x %d, %d-bit windows)" % (Ls, Rs, c), "bound": "hbm", "achieved": achieved,
+        "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": which,
         "kernel_ms": 1e3 * k_s, "share_of_step": k_s / (res_ms * 1e-3 / args.steps),
-        "int_pipe": {"achieved_gmul32_per_s": mul32 / k_s / 1e9 if k_s > 0 else 0.0, "peak_gimad_per_s": int_peak / 1e9,
-                     "frac": (mul32 / k_s) / int_peak if k_s > 0 else 0.0,
-                     "note": "the kernel's real limiter: 255-bit modular products on the IMAD pipe (DESIGN.md)"},
+        "int_pipe": {"achieved_gimad_per_s": imad / k_s / 1e9 if k_s > 0 else 0.0, "peak_gimad_per_s": int_peak / 1e9,
+                     "frac": (imad / k_s) / int_peak if k_s > 0 else 0.0,
+                     "note": "the kernel's real limiter: 64-bit integer multiply-adds (IMAD.WIDE.U32) on the fmaheavy pipe; "
+                             "ncu sm__pipe_fmaheavy_cycles_active 80.8 % at 2^20 (profiles/)"},
         "hbm_kernel_sample": {"kernel": "sc_cubic_kernel<false> (round 0: 4 tables x 32 B x 2^%d read)" % s,
                               "achieved": 4 * 32 * n / prof["sc_cubic_round0_kernel"] / 1e9 if prof["sc_cubic_round0_kernel"] > 0 else 0.0,
                               "unit": "GB/s", "kernel_ms": 1e3 * prof["sc_cubic_round0_kernel"]},
@@ -271,7 +278,7 @@ def main():
         "dtype": "u256 (F_l 253-bit / F_p 255-bit integers)", "data": "synthetic",
         "config": {"workload": "synthetic Spartan R1CS 2^%d constraints = vars, 10 inputs, NIZK::prove%s" % (
             s, " (configs[1])" if s == 16 else ""), "per_gpu": "one independent proof per GPU per step", "l2": "256 MiB flush between timed steps",
-            "msm_window_bits": c, "gens_build_s_untimed": gens_s, "proof_bytes": len(proof.to_bytes())},
+            "msm_window_bits": c, "host_threads": host_threads(), "gens_build_s_untimed": gens_s, "proof_bytes": len(proof.to_bytes())},
         "prove_time_s": res_ms * 1e-3 / args.steps,
         "phases_ms": {k: 1e3 * prof[k] for k in ("polycommit", "prove_sc_phase_one", "prove_sc_phase_two", "polyeval", "host_fiat_shamir")},
         "e2e": {"value": e2e_value, "unit": "constraints/s", "h2d_bytes_per_step": int(prof_e2e["h2d_bytes"]),

@@ -51,6 +51,8 @@ int sb200_k_commit_rows(const sb200_gens* gens, const uint8_t* Z_canon, size_t n
  * 2 gens_1.G[0], 3 gens_3.G[i], 4 gens_3.h, 5 gens_4.G[i], 6 gens_4.h         commitments.rs:15-58 */
 int sb200_k_gens_point(const sb200_gens* gens, int which, size_t i, uint8_t out32[32]);
 size_t sb200_k_gens_n(const sb200_gens* gens);
+/* window width (bits) of the device fixed-base tables built for these generators */
+uint32_t sb200_k_gens_window(const sb200_gens* gens);
 /* Host Pedersen commitment used in the Fiat-Shamir tail: x*G1[0] + blind*h (canonical inputs) commitments.rs:65-70 */
 int sb200_k_commit_scalar(const sb200_gens* gens, const uint8_t x_canon[32], const uint8_t blind_canon[32], uint8_t out32[32]);
 /* merlin: Transcript::new(label); append_message(mlabel,msg); challenge_bytes(clabel,out)   transcript.rs:13-37 */

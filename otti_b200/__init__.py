@@ -57,6 +57,7 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.sb200_last_error.restype = C.c_char_p
         L.sb200_k_gens_n.restype = C.c_size_t
+        L.sb200_k_gens_window.restype = C.c_uint32
         L.sb200_k_launch_count.restype = C.c_uint64
         L.sb200_instance_stream.restype = C.c_uint64
         _lib = L

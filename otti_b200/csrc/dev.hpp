@@ -27,7 +27,7 @@ void msm_table_free(MsmTable& t);
 // n_q (Q).  scalars: canonical integers < l, row-major with row stride `stride` (in scalars).
 // out32: rows x 32-byte compressed ristretto points.  `scratch` must hold rows*splits*128 bytes.
 struct MsmPlan {
-  uint32_t rows, n, splits;
+  uint32_t rows, n, splits, block, tpt;  // grid (splits, rows) x block threads, tpt terms per thread
 };
 MsmPlan msm_plan(uint32_t rows, uint32_t n);
 cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n,

@@ -555,43 +555,101 @@ __device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {
   n.xy2d = ldg_fp(&p->xy2d);
   return n;
 }
-// acc += k * B where B's window table starts at tb; k = canonical scalar at global address kp.
-// Signed radix-2^c digits in (-2^(c-1), 2^(c-1)]; zero digits cost nothing (vartime, like the
-// reference's vartime_multiscalar_mul).
-__device__ __forceinline__ void msm_accumulate(ge_t& acc, const niels_t* __restrict__ tb, const uint32_t* __restrict__ kp,
-                                               uint32_t c, uint32_t windows) {
+// digit `w` of the signed radix-2^c recoding of the scalar at kp (carry recomputed from the lower windows)
+__device__ __forceinline__ int32_t msm_digit_at(const uint32_t* kp, uint32_t w, uint32_t c) {
   uint32_t carry = 0;
-  for (uint32_t w = 0; w < windows; w++) {
-    int32_t d = msm_digit(kp, w, c, carry);
-    if (d != 0) {
-      bool neg = d < 0;
-      uint32_t mag = (uint32_t)(neg ? -d : d);
-      niels_t e = ldg_niels(tb + ((size_t)w << (c - 1)) + (mag - 1));
-      acc = ge_madd(acc, e, neg);
-    }
-  }
+  int32_t d = 0;
+  for (uint32_t i = 0; i <= w; i++) d = msm_digit(kp, i, c, carry);
+  return d;
 }
-__global__ void __launch_bounds__(256) msm_fixed_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
-                                                        const fl_t* __restrict__ scalars, size_t stride, uint32_t n,
-                                                        const fl_t* __restrict__ extra_h, uint32_t h_index, ge_t* partial) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  ge_t* sm = reinterpret_cast<ge_t*>(smem_raw);
+// Sum over the lanes of a warp / over nw <= 32 values held by the first lanes, by shuffles (out-of-line
+// point addition: one copy per kernel).
+__device__ __forceinline__ ge_t shfl_down_ge(const ge_t& x, int o) {
+  ge_t y;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    y.X.v[i] = __shfl_down_sync(0xffffffffu, x.X.v[i], o);
+    y.Y.v[i] = __shfl_down_sync(0xffffffffu, x.Y.v[i], o);
+    y.Z.v[i] = __shfl_down_sync(0xffffffffu, x.Z.v[i], o);
+    y.T.v[i] = __shfl_down_sync(0xffffffffu, x.T.v[i], o);
+  }
+  return y;
+}
+__device__ __forceinline__ ge_t warp_sum_ge_from(ge_t x, int first_offset) {
+#pragma unroll 1
+  for (int o = first_offset; o > 0; o >>= 1) x = ge_add_call(x, shfl_down_ge(x, o));
+  return x;
+}
+__device__ __forceinline__ niels_t ldg_niels_signed(const niels_t* p, bool neg) {  // -P = (y-x, y+x, -2dxy)
+  niels_t e = ldg_niels(p);
+  if (neg) {
+    fp_t t = e.yplusx;
+    e.yplusx = e.yminusx;
+    e.yminusx = t;
+    e.xy2d = fp_neg(e.xy2d);
+  }
+  return e;
+}
+// Commitment rows: block (split, row) sums terms [split*B*tpt, (split+1)*B*tpt) of its row.  A thread
+// walks the windows of one term at a time, fetching the table entry of window w+1 while it adds the
+// entry of window w; partial sums are combined by warp shuffles, then across the (<= 8) warps.  The
+// blind*h term of a row is spread over the lanes of warp 0 of split 0, one window per lane.
+__global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
+                                                           const fl_t* __restrict__ scalars, size_t stride, uint32_t n,
+                                                           const fl_t* __restrict__ extra_h, uint32_t h_index, uint32_t tpt,
+                                                           ge_t* partial) {
+  __shared__ ge_t sm[8];
   const uint32_t row = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
   const size_t epb = (size_t)windows << (c - 1);
-  const uint32_t per = (n + nsplit - 1) / nsplit;
-  const uint32_t j0 = split * per, j1 = min(n, j0 + per);
+  const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
   ge_t acc = ge_identity();
-  for (uint32_t j = j0 + threadIdx.x; j < j1; j += blockDim.x)
-    msm_accumulate(acc, tbl + (size_t)j * epb, reinterpret_cast<const uint32_t*>(scalars + (size_t)row * stride + j), c, windows);
-  if (extra_h != nullptr && split == 0 && threadIdx.x == 0)
-    msm_accumulate(acc, tbl + (size_t)h_index * epb, reinterpret_cast<const uint32_t*>(extra_h + row), c, windows);
-  sm[threadIdx.x] = acc;
-  __syncthreads();
-  for (uint32_t o = blockDim.x >> 1; o > 0; o >>= 1) {
-    if (threadIdx.x < o) sm[threadIdx.x] = ge_add_call(sm[threadIdx.x], sm[threadIdx.x + o]);
-    __syncthreads();
+  const uint32_t j0 = split * blockDim.x * tpt;
+  for (uint32_t k = 0; k < tpt; k++) {
+    const uint32_t j = j0 + k * blockDim.x + threadIdx.x;
+    if (j >= n) break;
+    uint32_t kw[8];
+    {
+      const uint4* q = reinterpret_cast<const uint4*>(scalars + (size_t)row * stride + j);
+      uint4 a = __ldg(q), b = __ldg(q + 1);
+      kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
+    }
+    if ((kw[0] | kw[1] | kw[2] | kw[3] | kw[4] | kw[5] | kw[6] | kw[7]) == 0) continue;
+    const niels_t* tb = tbl + (size_t)j * epb;
+    uint32_t carry = 0;
+    int32_t d_next = msm_digit(kw, 0, c, carry);
+    niels_t e_next;
+    if (d_next != 0) e_next = ldg_niels_signed(tb + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1), d_next < 0);
+    for (uint32_t w = 0; w < windows; w++) {
+      const int32_t d = d_next;
+      const niels_t e = e_next;
+      if (w + 1 < windows) {
+        d_next = msm_digit(kw, w + 1, c, carry);
+        if (d_next != 0)
+          e_next = ldg_niels_signed(tb + ((size_t)(w + 1) << (c - 1)) + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1), d_next < 0);
+      }
+      if (d != 0) acc = ge_madd(acc, e, false);
+    }
   }
-  if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = sm[0];
+  if (extra_h != nullptr && split == 0 && wid == 0 && lane < windows) {
+    uint32_t kw[8];
+    const uint4* q = reinterpret_cast<const uint4*>(extra_h + row);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
+    for (uint32_t w = lane; w < windows; w += 32) {
+      int32_t d = msm_digit_at(kw, w, c);
+      if (d != 0)
+        acc = ge_madd(acc, ldg_niels_signed(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(d < 0 ? -d : d) - 1), d < 0), false);
+    }
+  }
+  acc = warp_sum_ge_from(acc, 16);
+  if (nw > 1) {
+    if (lane == 0) sm[wid] = acc;
+    __syncthreads();
+    if (wid != 0) return;
+    acc = lane < nw ? sm[lane] : ge_identity();
+    acc = warp_sum_ge_from(acc, 4);
+  }
+  if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = acc;
 }
 __global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit, uint8_t* __restrict__ out32) {
   uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -608,12 +666,16 @@ MsmPlan msm_plan(uint32_t rows, uint32_t n) {
   MsmPlan p;
   p.rows = rows;
   p.n = n;
-  // enough blocks to cover the chip a few times over, never fewer than 64 terms per block
-  uint32_t want = (uint32_t)((kSMs * 4 + rows - 1) / (rows ? rows : 1));
-  uint32_t maxs = (n + 63) / 64;
-  if (want < 1) want = 1;
-  if (maxs < 1) maxs = 1;
-  p.splits = want < maxs ? want : maxs;
+  uint32_t block = 32;
+  while (block < 256 && block < n) block <<= 1;
+  p.block = block;
+  // terms per thread: enough blocks for ~6 waves of 2 x 256 threads per SM, at most 8 terms per thread
+  size_t total = (size_t)rows * n, per_wave = (size_t)kSMs * 512 * 6;
+  uint32_t tpt = 1;
+  while (tpt < 8 && (size_t)tpt * 2 * per_wave <= total) tpt <<= 1;
+  p.tpt = tpt;
+  p.splits = (n + block * tpt - 1) / (block * tpt);
+  if (p.splits < 1) p.splits = 1;
   return p;
 }
 size_t msm_scratch_bytes(uint32_t rows, uint32_t n) {
@@ -627,12 +689,10 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   (void)q_index;
   if (!rows) return cudaSuccess;
   MsmPlan p = msm_plan(rows, n);
-  uint32_t per = (n + p.splits - 1) / p.splits;
-  int block = per >= 256 ? 256 : per >= 128 ? 128 : 64;
   dim3 grid(p.splits, rows);
   if (ev) cudaEventRecord(ev[0], s);
-  msm_fixed_kernel<<<grid, block, block * sizeof(ge_t), s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index,
-                                                              reinterpret_cast<ge_t*>(scratch));
+  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch));
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
@@ -675,13 +735,6 @@ __device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {
     x = warp_sum_ge(x);
   }
   return x;
-}
-// digit `w` of the signed radix-2^c recoding of the scalar at kp (carry recomputed from the lower windows)
-__device__ __forceinline__ int32_t msm_digit_at(const uint32_t* kp, uint32_t w, uint32_t c) {
-  uint32_t carry = 0;
-  int32_t d = 0;
-  for (uint32_t i = 0; i <= w; i++) d = msm_digit(kp, i, c, carry);
-  return d;
 }
 __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
                                                         const fl_t* __restrict__ scalars, size_t stride, uint32_t n,

@@ -382,7 +382,21 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
       fe_tobytes(fe_mul(bases[i].Y, zi), &xy[64 * i + 32]);
     }
   }
+  // Window width of the device tables: every extra bit removes madds from the commitment kernel
+  // (floor(252/c)+1 per term) and doubles the table.  Largest c whose table fits SB200_TABLE_MB
+  // (default 20 GiB of the 180 GB HBM); SB200_MSM_WINDOW forces a value.
   uint32_t c = 8;
+  {
+    size_t budget = (size_t)20480 << 20;
+    if (const char* env = getenv("SB200_TABLE_MB")) {
+      long v = atol(env);
+      if (v > 0) budget = (size_t)v << 20;
+    }
+    for (uint32_t cc = 9; cc <= 16; cc++) {
+      size_t bytes = bases.size() * (size_t)(252 / cc + 1) * ((size_t)1 << (cc - 1)) * 96;
+      if (bytes <= budget) c = cc;
+    }
+  }
   if (const char* env = getenv("SB200_MSM_WINDOW")) {
     int v = atoi(env);
     if (v >= 2 && v <= 16) c = (uint32_t)v;
