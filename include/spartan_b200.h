@@ -54,7 +54,8 @@ enum {
   /* backend */
   SB200_ERR_NO_DEVICE = -100,
   SB200_ERR_CUDA = -101,
-  SB200_ERR_ARG = -102
+  SB200_ERR_ARG = -102,
+  SB200_ERR_COMM = -103
 };
 
 /*
@@ -100,6 +101,17 @@ typedef struct sb200_comm_vt {
   int (*allgather)(void* ctx, const void* send, size_t bytes, void* recv);
 } sb200_comm_vt;
 
+/* Exchange over a POSIX shared-memory segment for ranks on ONE box (the 8 x B200 node of north_star): fills
+ * *out with a hook whose allgather costs ~1 us.  Collective: every rank calls it with the same name, which must
+ * be unique to the job (a stale segment of the same name must not exist).  Hosts spanning boxes supply their own
+ * hook (NCCL / torch.distributed: otti_b200/comm.py). */
+int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out);
+void sb200_comm_shm_close(sb200_comm_vt* comm);
+/* Host-only self-test of a hook (no GPU): `rounds` all-gathers of 3 scalars per rank, summed mod l as a sharded
+ * sum-check round does; the digest must equal sb200_comm_selftest_expected(world, rounds) on every rank. */
+int sb200_comm_selftest(const sb200_comm_vt* comm, int rounds, uint8_t digest32_out[32]);
+int sb200_comm_selftest_expected(int world, int rounds, uint8_t digest32_out[32]);
+
 /* Selects the CUDA device for the calling process (one process per GPU).
  * Fails with SB200_ERR_NO_DEVICE if it is not compute capability 10.x. */
 int sb200_init(int device);
@@ -113,6 +125,17 @@ int sb200_assignment_check(const uint8_t* vals32, uint64_t n);
 int sb200_instance_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
                        const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
                        sb200_instance** out);
+
+/* The same constructor for ONE PROOF SHARDED over world = 2, 4 or 8 GPUs (one process per GPU; every rank passes
+ * the same matrices).  This rank keeps the constraint rows i = rank (mod world) as CSR and the z columns
+ * j = rank (mod world) as CSC.  sb200_nizk_prove on such an instance needs a sb200_comm_vt
+ * with the same rank/world; all ranks call it with identical arguments and obtain identical proofs.
+ * SB200_ERR_ARG if the instance is too small to give every rank two rows, two columns and one commitment row. */
+int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
+                               const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
+                               int rank, int world, sb200_instance** out);
+int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t seed, int rank,
+                                     int world, sb200_instance** out, uint8_t* vars32_out, uint8_t* inputs32_out);
 
 /* Instance::produce_synthetic_r1cs(num_cons, num_vars, num_inputs)       lib.rs:260-271
  * OsRng is replaced by SplitMix64(seed) so runs are reproducible.  vars32_out

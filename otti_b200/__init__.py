@@ -192,20 +192,21 @@ class Instance:
         self.num_cons, self.num_vars, self.num_inputs = int(d[0]), int(d[1]), int(d[2])
 
     @staticmethod
-    def new(num_cons, num_vars, num_inputs, A, B, Cm):
-        """`Instance::new` (lib.rs:121-225); raises R1CSError("InvalidIndex" | "InvalidScalar")."""
+    def new(num_cons, num_vars, num_inputs, A, B, Cm, rank=0, world=1):
+        """`Instance::new` (lib.rs:121-225); raises R1CSError("InvalidIndex" | "InvalidScalar").
+        world > 1: this process holds shard `rank` of one proof sharded over `world` GPUs."""
         parts = [_coo(M) for M in (A, B, Cm)]
         rows = (C.c_void_p * 3)(*[p[1] for p in parts])
         cols = (C.c_void_p * 3)(*[p[2] for p in parts])
         vals = (C.c_void_p * 3)(*[p[3] for p in parts])
         nnz = (C.c_uint64 * 3)(*[p[0] for p in parts])
         h = C.c_void_p()
-        _check(lib().sb200_instance_new(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs), rows, cols, vals,
-                                        nnz, C.byref(h)))
+        _check(lib().sb200_instance_new_sharded(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs), rows, cols,
+                                                vals, nnz, C.c_int(rank), C.c_int(world), C.byref(h)))
         return Instance(h)
 
     @staticmethod
-    def produce_synthetic_r1cs(num_cons, num_vars, num_inputs, seed=0x0771, pinned=False):
+    def produce_synthetic_r1cs(num_cons, num_vars, num_inputs, seed=0x0771, pinned=False, rank=0, world=1):
         """`Instance::produce_synthetic_r1cs` (lib.rs:260-271) with a seeded PRNG in place of OsRng.
         Returns (Instance, VarsAssignment, InputsAssignment)."""
         if pinned:
@@ -220,8 +221,8 @@ class Instance:
         vp = C.c_void_p(vbuf.data_ptr()) if pinned else C.cast(vbuf, C.c_void_p)
         ip = C.c_void_p(ibuf.data_ptr()) if pinned else C.cast(ibuf, C.c_void_p)
         h = C.c_void_p()
-        _check(lib().sb200_instance_synthetic(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
-                                              C.c_uint64(seed), C.byref(h), vp, ip))
+        _check(lib().sb200_instance_synthetic_sharded(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
+                                                      C.c_uint64(seed), C.c_int(rank), C.c_int(world), C.byref(h), vp, ip))
         if pinned:
             v, i = vbuf[:num_vars * 32], ibuf[:num_inputs * 32]
         else:
@@ -277,9 +278,10 @@ class NIZK:
         self.bytes = proof_bytes
 
     @staticmethod
-    def prove(inst, vars_, inputs, gens, transcript, tape_seed64=None, resident=False):
+    def prove(inst, vars_, inputs, gens, transcript, tape_seed64=None, resident=False, comm=None):
         """`NIZK::prove(&inst, vars, &inputs, &gens, &mut transcript)` (lib.rs:493-535).
-        tape_seed64 (64 bytes) pins the RandomTape seed for reproducible proofs; None = OS randomness."""
+        tape_seed64 (64 bytes) pins the RandomTape seed for reproducible proofs; None = OS randomness.
+        comm: exchange hook (otti_b200.comm) when `inst` is one shard of a proof spread over several GPUs."""
         vp, vk = (None, None) if resident else _ptr(vars_.data)
         ip, ik = _ptr(inputs.data)
         sp, sk = _ptr(tape_seed64)
@@ -289,7 +291,8 @@ class NIZK:
         out = C.POINTER(C.c_uint8)()
         n = C.c_size_t(0)
         _check(lib().sb200_nizk_prove(inst.h, vp, C.c_uint64(vars_.n), ip, C.c_uint64(inputs.n), gens.h, C.byref(vt), None,
-                                      C.c_size_t(0), sp, None, C.byref(out), C.byref(n)))
+                                      C.c_size_t(0), sp, C.byref(comm.vt) if comm is not None else None, C.byref(out),
+                                      C.byref(n)))
         b = C.string_at(out, n.value)
         lib().sb200_free(out)
         return NIZK(b)

@@ -33,6 +33,11 @@ MsmPlan msm_plan(uint32_t rows, uint32_t n);
 cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n,
                       const fl_t* extra_h, const fl_t* extra_q, uint32_t h_index, uint32_t q_index, void* scratch,
                       uint8_t* out32, cudaStream_t s, cudaEvent_t* ev = nullptr);  // ev[0..1] bracket the main kernel
+// Two-step form: row sums without any blind term, then (partials + extra_h[row]*base[h_index]) -> compressed.
+cudaError_t msm_fixed_rows(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, void* scratch,
+                           cudaStream_t s, cudaEvent_t* ev = nullptr);
+cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const fl_t* extra_h, uint32_t h_index,
+                             const void* scratch, uint8_t* out32, cudaStream_t s);
 size_t msm_scratch_bytes(uint32_t rows, uint32_t n);
 // Latency-oriented variant for a few rows (bullet reduction, one-row commitments): every (term, window)
 // pair is a unit of work, the sum is left UNCOMPRESSED in out_ext[rows] (extended coordinates X,Y,Z,T as
@@ -59,6 +64,10 @@ cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, u
 // eq(r) table of length 2^ell                                         (dense_mlpoly.rs:67-83)
 // r: device array of ell Montgomery scalars; tmp: >= 2^ceil(ell/2)+2^floor(ell/2) scalars
 cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s);
+// the same table with every entry multiplied by `init` (Montgomery)
+cudaError_t k_eq_table_scaled(const fl_t* r, uint32_t ell, fl_t init, fl_t* out, fl_t* tmp, cudaStream_t s);
+// out[i] = in[i*step + first], i < n
+cudaError_t k_gather_stride(const fl_t* in, size_t n, size_t step, size_t first, fl_t* out, cudaStream_t s);
 
 struct Csr {  // three matrices share the layout
   const uint32_t* ptr[3];

@@ -63,12 +63,13 @@ struct SparseDev {  // CSR (by row) or CSC (by column) of the three matrices
 struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   bool ready = false;
   uint64_t resident_vars = ~0ull;  // witness length placed by sb200_witness_upload
-  DevBuf<sb::fl_t> vars_canon, varsM, z, abc, T, A, B, C, eq_tmp, sc_partials, small, blinds, bound_tmp, LZ, bl_a, bl_b,
+  DevBuf<sb::fl_t> vars_canon, varsM, z, zloc, abc, T, A, B, C, eq_tmp, sc_partials, small, blinds, bound_tmp, LZ, bl_a, bl_b,
       coeff0, coeff1, srows;
   DevBuf<unsigned int> counter;
   DevBuf<uint32_t> flag;
   DevBuf<uint8_t> msm_scratch, pts;
   uint8_t* pinned = nullptr;  // host staging
+  uint8_t* blind_stage = nullptr;  // pinned staging of the commitment blinds (canonical | Montgomery)
   size_t pinned_bytes = 0;
   uint8_t* mail = nullptr;      // mapped pinned mailbox the kernels write round results + flags into (prover.inc Mail)
   uint8_t* mail_dev = nullptr;  // the same memory as seen from the device
@@ -78,6 +79,7 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   ~Workspace() {
     for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);
     if (pinned) cudaFreeHost(pinned);
+    if (blind_stage) cudaFreeHost(blind_stage);
     if (mail) cudaFreeHost(mail);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -86,6 +88,11 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
 struct Instance {
   uint64_t num_cons = 0, num_vars = 0, num_inputs = 0;  // padded, lib.rs:130-158
   uint64_t nnz[3] = {0, 0, 0};
+  // One proof sharded over world = 2^gamma GPUs: this rank holds the CSR of the constraint
+  // rows i = rank (mod world) (local row i >> gamma, global column indices) and the CSC of the z columns
+  // j = rank (mod world) (local column j >> gamma, global row indices).  world == 1: the whole matrices.
+  int rank = 0, world = 1;
+  uint32_t gamma = 0;
   SparseDev csr, csc;
   mutable Workspace ws;
 };

@@ -84,7 +84,11 @@ class HostPool {
   static HostPool& get() {
     static HostPool* pool = [] {
       int hw = (int)std::thread::hardware_concurrency();
-      int n = hw > 2 ? hw - 2 : 0;
+      if (const char* lw = getenv("LOCAL_WORLD_SIZE")) {  // one process per GPU (torchrun): share the host cores
+        int ranks = atoi(lw);
+        if (ranks > 1) hw /= ranks;
+      }
+      int n = hw > 2 ? hw - 2 : (hw == 2 ? 1 : 0);  // with two cores: this thread + the tape drawer
       if (n > 6) n = 6;
       if (const char* e = getenv("SB200_HOST_THREADS")) n = atoi(e);
       if (n < 0) n = 0;

@@ -214,10 +214,12 @@ cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, u
 // ------------------------------------------------------------------ eq table
 // E[i] = prod_j (bit_{ell-1-j}(i) ? r[j] : 1 - r[j])  -- thread per entry, used for the two
 // half-size factor tables (<= 2^12 entries each).
-__global__ void eq_small_kernel(const fl_t* __restrict__ r, uint32_t ell, fl_t* __restrict__ out) {
+// `init` (Montgomery) multiplies every entry: 1 for a plain table; a sharded prover passes the factor
+// contributed by the index bits its rank fixes.
+__global__ void eq_small_kernel(const fl_t* __restrict__ r, uint32_t ell, fl_t init, fl_t* __restrict__ out) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (1u << ell)) return;
-  fl_t acc = fl_one(), one = fl_one();
+  fl_t acc = init, one = fl_one();
   for (uint32_t j = 0; j < ell; j++) {
     fl_t rj = ldg_fl(r + j);
     bool bit = (i >> (ell - 1 - j)) & 1u;
@@ -232,22 +234,35 @@ __global__ void eq_outer_kernel(const fl_t* __restrict__ hi, const fl_t* __restr
   const size_t mask = ((size_t)1 << b) - 1;
   for (; i < n; i += stride) st_fl(out + i, fl_mul(ldg_fl(hi + (i >> b)), ldg_fl(lo + (i & mask))));
 }
-cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s) {
+cudaError_t k_eq_table_scaled(const fl_t* r, uint32_t ell, fl_t init, fl_t* out, fl_t* tmp, cudaStream_t s) {
   if (ell <= 8) {
-    eq_small_kernel<<<((1u << ell) + 127) / 128, 128, 0, s>>>(r, ell, out);
+    eq_small_kernel<<<((1u << ell) + 127) / 128, 128, 0, s>>>(r, ell, init, out);
     return SB_LAUNCHED();
   }
   uint32_t a = ell / 2, b = ell - a;  // high a variables (r[0..a)), low b variables
   fl_t* hi = tmp;
   fl_t* lo = tmp + ((size_t)1 << a);
-  eq_small_kernel<<<((1u << a) + 127) / 128, 128, 0, s>>>(r, a, hi);
+  eq_small_kernel<<<((1u << a) + 127) / 128, 128, 0, s>>>(r, a, init, hi);
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  eq_small_kernel<<<((1u << b) + 127) / 128, 128, 0, s>>>(r + a, b, lo);
+  eq_small_kernel<<<((1u << b) + 127) / 128, 128, 0, s>>>(r + a, b, fl_one(), lo);
   e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
   size_t n = (size_t)1 << ell;
   eq_outer_kernel<<<grid_for(n, 256), 256, 0, s>>>(hi, lo, b, n, out);
+  return SB_LAUNCHED();
+}
+cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s) {
+  return k_eq_table_scaled(r, ell, fl_one(), out, tmp, s);
+}
+// out[i] = in[i * step + first]: a rank's cyclic slice of a full-length table
+__global__ void gather_stride_kernel(const fl_t* __restrict__ in, size_t n, size_t step, size_t first, fl_t* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) st_fl(out + i, ldg_fl(in + i * step + first));
+}
+cudaError_t k_gather_stride(const fl_t* in, size_t n, size_t step, size_t first, fl_t* out, cudaStream_t s) {
+  if (!n) return cudaSuccess;
+  gather_stride_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, n, step, first, out);
   return SB_LAUNCHED();
 }
 
@@ -651,11 +666,32 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
   }
   if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = acc;
 }
-__global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit, uint8_t* __restrict__ out32) {
+// Sums the per-split partials of a row, optionally adds the row's blind*h term (one table look-up per window --
+// kept out of the row kernel so that the commitment can start before the RandomTape has produced the blinds),
+// and compresses.
+__global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit, uint8_t* __restrict__ out32,
+                                  const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows, const fl_t* __restrict__ extra_h,
+                                  uint32_t h_index) {
   uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= rows) return;
   ge_t acc = partial[(size_t)row * nsplit];
   for (uint32_t s = 1; s < nsplit; s++) acc = ge_add_call(acc, partial[(size_t)row * nsplit + s]);
+  if (extra_h != nullptr) {
+    const size_t epb = (size_t)windows << (c - 1);
+    uint32_t kw[8];
+    const uint4* q = reinterpret_cast<const uint4*>(extra_h + row);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < windows; w++) {
+      int32_t d = msm_digit(kw, w, c, carry);
+      if (d != 0) {
+        bool neg = d < 0;
+        niels_t e = ldg_niels(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(neg ? -d : d) - 1));
+        acc = ge_madd_call(acc, e, neg);
+      }
+    }
+  }
   uint32_t w[8];
   ge_compress_t<FpCall>(acc, w);
   uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
@@ -696,7 +732,29 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
-  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32);
+  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c,
+                                                    t.windows, nullptr, 0);
+  return SB_LAUNCHED();
+}
+// The same in two halves: the row sums first (no blinds needed), then blind*h + compression.
+cudaError_t msm_fixed_rows(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, void* scratch,
+                           cudaStream_t s, cudaEvent_t* ev) {
+  if (!rows) return cudaSuccess;
+  MsmPlan p = msm_plan(rows, n);
+  dim3 grid(p.splits, rows);
+  if (ev) cudaEventRecord(ev[0], s);
+  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, nullptr, 0, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch));
+  cudaError_t e = SB_LAUNCHED();
+  if (ev) cudaEventRecord(ev[1], s);
+  return e;
+}
+cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const fl_t* extra_h, uint32_t h_index, const void* scratch,
+                             uint8_t* out32, cudaStream_t s) {
+  if (!rows) return cudaSuccess;
+  MsmPlan p = msm_plan(rows, n);
+  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c,
+                                                    t.windows, extra_h, h_index);
   return SB_LAUNCHED();
 }
 

@@ -76,20 +76,29 @@ struct CooEntry {
 };
 
 static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint64_t ncols, Instance& inst) {
+  const uint32_t g = (uint32_t)inst.world, k = (uint32_t)inst.rank, sh = inst.gamma;
   for (int orient = 0; orient < 2; orient++) {
     SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
-    uint64_t nseg = orient == 0 ? nrows : ncols;
+    const uint64_t nseg = (orient == 0 ? nrows : ncols) >> sh;  // segments (rows or columns) this rank owns
     for (int m = 0; m < 3; m++) {
-      size_t nnz = M[m].size();
-      std::vector<uint32_t> ptr(nseg + 1, 0), idx(nnz);
+      std::vector<uint32_t> ptr(nseg + 1, 0);
+      size_t nnz = 0;
+      for (const CooEntry& e : M[m]) {
+        uint32_t key = orient == 0 ? e.row : e.col;
+        if ((key & (g - 1)) != k) continue;
+        ptr[(key >> sh) + 1]++;
+        nnz++;
+      }
+      std::vector<uint32_t> idx(nnz);
       std::vector<Fl> val(nnz);
-      for (const CooEntry& e : M[m]) ptr[(orient == 0 ? e.row : e.col) + 1]++;
       for (uint64_t i = 0; i < nseg; i++) ptr[i + 1] += ptr[i];
       std::vector<uint32_t> fill(ptr.begin(), ptr.end() - 1);
       for (const CooEntry& e : M[m]) {
-        uint32_t k = fill[orient == 0 ? e.row : e.col]++;
-        idx[k] = orient == 0 ? e.col : e.row;
-        val[k] = e.val;
+        uint32_t key = orient == 0 ? e.row : e.col;
+        if ((key & (g - 1)) != k) continue;
+        uint32_t at = fill[key >> sh]++;
+        idx[at] = orient == 0 ? e.col : e.row;  // the other coordinate stays global
+        val[at] = e.val;
       }
       SB_CUDA(sd.ptr[m].alloc(nseg + 1));
       SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
@@ -100,6 +109,22 @@ static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint6
         SB_CUDA(cudaMemcpy(sd.val[m].p, val.data(), nnz * 32, cudaMemcpyHostToDevice));
       }
     }
+  }
+  return SB200_OK;
+}
+// world must be 1, 2, 4 or 8 and leave every rank at least two constraint rows, two z columns and one commitment row
+static int shard_check(int rank, int world, uint64_t ncp, uint64_t nvp, uint32_t& gamma) {
+  gamma = 0;
+  if (world < 1 || (world & (world - 1)) || world > 8 || rank < 0 || rank >= world) {
+    set_error("sharding: world must be 1, 2, 4 or 8 and 0 <= rank < world");
+    return SB200_ERR_ARG;
+  }
+  while ((1 << gamma) < world) gamma++;
+  uint64_t ell = 0;
+  while (((uint64_t)1 << (ell + 1)) <= nvp) ell++;
+  if (world > 1 && (ncp < 2ull * world || 2 * nvp < 2ull * world || ((uint64_t)1 << (ell / 2)) < (uint64_t)world)) {
+    set_error("sharding: instance too small for this many GPUs");
+    return SB200_ERR_ARG;
   }
   return SB200_OK;
 }
@@ -142,9 +167,9 @@ int sb200_init(int device) {
   return ensure_device();
 }
 
-int sb200_instance_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
-                       const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
-                       sb200_instance** out) {
+int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
+                               const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
+                               int rank, int world, sb200_instance** out) {
   if (!out) return SB200_ERR_ARG;
   *out = nullptr;
   uint64_t ncp, nvp;
@@ -168,15 +193,24 @@ int sb200_instance_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs
     }
     // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product.
   }
-  int rc = ensure_device();
+  uint32_t gamma = 0;
+  int rc = shard_check(rank, world, ncp, nvp, gamma);
+  if (rc) return rc;
+  rc = ensure_device();
   if (rc) return rc;
   Instance* inst = new Instance();
   inst->num_cons = ncp; inst->num_vars = nvp; inst->num_inputs = num_inputs;
+  inst->rank = rank; inst->world = world; inst->gamma = gamma;
   for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].size();
   rc = upload_sparse(M, ncp, 2 * nvp, *inst);
   if (rc) { delete inst; return rc; }
   *out = reinterpret_cast<sb200_instance*>(inst);
   return SB200_OK;
+}
+int sb200_instance_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
+                       const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],
+                       sb200_instance** out) {
+  return sb200_instance_new_sharded(num_cons, num_vars, num_inputs, rows, cols, vals32, nnz, 0, 1, out);
 }
 
 static inline uint64_t splitmix64(uint64_t& s) {
@@ -188,8 +222,8 @@ static inline uint64_t splitmix64(uint64_t& s) {
 }
 
 // R1CSInstance::produce_synthetic_r1cs, r1csinstance.rs:136-214
-int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t seed,
-                             sb200_instance** out, uint8_t* vars32_out, uint8_t* inputs32_out) {
+int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t seed, int rank,
+                                     int world, sb200_instance** out, uint8_t* vars32_out, uint8_t* inputs32_out) {
   if (!out) return SB200_ERR_ARG;
   *out = nullptr;
   auto pow2 = [](uint64_t x) { return x && !(x & (x - 1)); };
@@ -197,7 +231,10 @@ int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_
   if (!pow2(num_vars)) { set_error("NonPowerOfTwoVars"); return SB200_ERR_NON_POW2_VARS; }   // :147
   if (!(num_inputs < num_vars)) { set_error("assert num_inputs < num_vars"); return SB200_ERR_ASSERT; }  // :150
   if (num_cons >= (1ull << 31) || num_vars >= (1ull << 30)) return SB200_ERR_ARG;
-  int rc = ensure_device();
+  uint32_t gamma = 0;
+  int rc = shard_check(rank, world, num_cons, num_vars, gamma);
+  if (rc) return rc;
+  rc = ensure_device();
   if (rc) return rc;
   const uint64_t size_z = num_vars + num_inputs + 1;
   FlVec Z(size_z);
@@ -236,6 +273,7 @@ int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_
   }
   Instance* inst = new Instance();
   inst->num_cons = num_cons; inst->num_vars = num_vars; inst->num_inputs = num_inputs;
+  inst->rank = rank; inst->world = world; inst->gamma = gamma;
   for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].size();
   rc = upload_sparse(M, num_cons, 2 * num_vars, *inst);
   if (rc) { delete inst; return rc; }
@@ -243,6 +281,10 @@ int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_
   for (uint64_t i = 0; i < num_inputs; i++) fl_to_bytes(Z[num_vars + 1 + i], inputs32_out + 32 * i);
   *out = reinterpret_cast<sb200_instance*>(inst);
   return SB200_OK;
+}
+int sb200_instance_synthetic(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t seed,
+                             sb200_instance** out, uint8_t* vars32_out, uint8_t* inputs32_out) {
+  return sb200_instance_synthetic_sharded(num_cons, num_vars, num_inputs, seed, 0, 1, out, vars32_out, inputs32_out);
 }
 
 int sb200_assignment_check(const uint8_t* vals32, uint64_t n) {
@@ -291,6 +333,7 @@ int sb200_instance_is_sat(const sb200_instance* h, const uint8_t* vars32, uint64
   const Instance& inst = *reinterpret_cast<const Instance*>(h);
   if (n_vars > inst.num_vars) { set_error("InvalidNumberOfInputs"); return SB200_ERR_INVALID_NUMBER_OF_INPUTS; }      // lib.rs:233-235
   if (n_inputs != inst.num_inputs) { set_error("InvalidNumberOfInputs"); return SB200_ERR_INVALID_NUMBER_OF_INPUTS; }  // lib.rs:237-239
+  if (inst.world > 1) { set_error("is_sat needs an unsharded instance"); return SB200_ERR_ARG; }
   int rc = ensure_device();
   if (rc) return rc;
   const size_t Nv = inst.num_vars, Nc = inst.num_cons;
@@ -415,6 +458,7 @@ void sb200_gens_free(sb200_gens* h) { delete reinterpret_cast<Gens*>(h); }
 }  // extern "C"
 
 // =============================================================================== prover
+#include "host/comm.hpp"
 #include "host/pool.hpp"
 #include "host/tape.hpp"
 #include "prover.inc"
@@ -496,7 +540,6 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
                      size_t label_len, const uint8_t* tape_seed64, const sb200_comm_vt* comm, uint8_t** proof_out,
                      size_t* proof_len) {
   if (!hi || !hg || !proof_out || !proof_len || (!inputs32 && n_inputs)) return SB200_ERR_ARG;
-  if (comm && comm->world > 1) { set_error("sharded prove: use sb200_nizk_prove with world == 1 in this build"); return SB200_ERR_ARG; }
   int rc = ensure_device();
   if (rc) return rc;
   const Instance& inst = *reinterpret_cast<const Instance*>(hi);
@@ -514,10 +557,10 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
   try {
     if (transcript) {
       VtTranscript tr(transcript);
-      rc = prove_impl(inst, vars32, n_vars, inputs32, n_inputs, gens, tr, seed_scalar, pf);
+      rc = prove_impl(inst, vars32, n_vars, inputs32, n_inputs, gens, tr, seed_scalar, comm, pf);
     } else {
       MerlinTranscript tr(label, label_len);
-      rc = prove_impl(inst, vars32, n_vars, inputs32, n_inputs, gens, tr, seed_scalar, pf);
+      rc = prove_impl(inst, vars32, n_vars, inputs32, n_inputs, gens, tr, seed_scalar, comm, pf);
     }
   } catch (const std::exception& e) {
     set_error(std::string("exception: ") + e.what());
@@ -551,6 +594,67 @@ int sb200_witness_upload(const sb200_instance* hi, const sb200_gens* hg, const u
 // cudaStream_t the instance's kernels run on (for CUDA-event timing by the caller); 0 before the first prove
 uint64_t sb200_instance_stream(const sb200_instance* hi) {
   return hi ? (uint64_t)(uintptr_t) reinterpret_cast<const Instance*>(hi)->ws.stream : 0;
+}
+
+// ---- exchange for sharded proofs ------------------------------------------------------------
+int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out) {
+  if (!name || !out) return SB200_ERR_ARG;
+  ShmComm* c = new ShmComm();
+  int rc = c->open(name, rank, world);
+  if (rc) {
+    set_error("sb200_comm_shm_open failed (" + std::to_string(rc) + ")");
+    delete c;
+    return SB200_ERR_COMM;
+  }
+  out->ctx = c;
+  out->rank = rank;
+  out->world = world;
+  out->allgather = shm_allgather_thunk;
+  return SB200_OK;
+}
+void sb200_comm_shm_close(sb200_comm_vt* comm) {
+  if (!comm || !comm->ctx) return;
+  ShmComm* c = static_cast<ShmComm*>(comm->ctx);
+  c->close();
+  delete c;
+  comm->ctx = nullptr;
+}
+// Host-only check of an exchange hook (no GPU work): `rounds` all-gathers of three scalars per rank, summed mod l the
+// way a sharded sum-check round does and absorbed into a transcript; digest32_out must be the same on every rank
+// and equal to sb200_comm_selftest_expected(world, rounds).
+static Fl selftest_scalar(int rank, int round, int k) {
+  uint8_t wide[64];
+  for (int i = 0; i < 64; i++) wide[i] = (uint8_t)(i * 131 + rank * 17 + round * 29 + k * 43 + 1);
+  return fl_from_bytes_wide(wide);
+}
+int sb200_comm_selftest(const sb200_comm_vt* comm, int rounds, uint8_t digest32_out[32]) {
+  if (!comm || !comm->allgather || !digest32_out || comm->world < 1) return SB200_ERR_ARG;
+  MerlinTranscript tr("comm selftest", 13);
+  std::vector<uint8_t> recv((size_t)comm->world * 96);
+  for (int j = 0; j < rounds; j++) {
+    Fl mine[3];
+    for (int k = 0; k < 3; k++) mine[k] = selftest_scalar(comm->rank, j, k);
+    if (comm->allgather(comm->ctx, mine, 96, recv.data()) != 0) { set_error("allgather failed"); return SB200_ERR_COMM; }
+    for (int k = 0; k < 3; k++) {
+      Fl sum = fl_zero();
+      for (int q = 0; q < comm->world; q++) sum = fl_add(sum, from_dev_bytes(&recv[96 * (size_t)q + 32 * k]));
+      tr.append_scalar("sum", sum);
+    }
+  }
+  tr.challenge_bytes("digest", digest32_out, 32);
+  return SB200_OK;
+}
+int sb200_comm_selftest_expected(int world, int rounds, uint8_t digest32_out[32]) {
+  if (world < 1 || !digest32_out) return SB200_ERR_ARG;
+  MerlinTranscript tr("comm selftest", 13);
+  for (int j = 0; j < rounds; j++)
+    for (int k = 0; k < 3; k++) {
+      Fl sum = fl_zero();
+      for (int q = 0; q < world; q++) sum = fl_add(sum, selftest_scalar(q, j, k));
+      tr.append_scalar("sum", sum);
+    }
+  tr.challenge_bytes("digest", digest32_out, 32);
+  return SB200_OK;
 }
 
 int sb200_last_prove_profile(double out[12]) {

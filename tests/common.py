@@ -29,3 +29,25 @@ def unmont(b):
 
 def sha(b):
     return hashlib.sha256(b).hexdigest()
+
+
+def ragged_r1cs(nc, nv, ni):
+    """A satisfiable R1CS with non-power-of-two sizes, several entries per row, duplicate entries and the
+    constant column in use; returns (A, B, C, vars, inputs) with COO triples (row, col, 32 bytes)."""
+    rng = random.Random(nc * 1000 + nv)
+    vars_ = [rng.randrange(ELL) for _ in range(nv)]
+    inputs = [rng.randrange(ELL) for _ in range(ni)]
+    z = vars_ + [1] + inputs
+    ncols = len(z)
+    A, B, Cm = [], [], []
+    for row in range(nc):
+        ra = [(rng.randrange(ncols), rng.choice([1, 2, ELL - 1, rng.randrange(ELL)])) for _ in range(rng.choice([1, 2, 3]))]
+        rb = [(rng.randrange(ncols), rng.choice([1, rng.randrange(2**20)])) for _ in range(rng.choice([1, 2]))]
+        if row % 7 == 0:
+            ra.append((nv, 5))  # the constant column
+        az = sum(v * z[c] for c, v in ra) % ELL
+        bz = sum(v * z[c] for c, v in rb) % ELL
+        A += [(row, c, v.to_bytes(32, "little")) for c, v in ra]
+        B += [(row, c, v.to_bytes(32, "little")) for c, v in rb]
+        Cm.append((row, nv, (az * bz % ELL).to_bytes(32, "little")))
+    return A, B, Cm, vars_, inputs
