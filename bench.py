@@ -41,6 +41,9 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log-size", type=int, default=16, help="log2 of constraints = vars (configs[1] = 16)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard-log-size", type=int, default=22,
+                    help="N > 1: log2 size of the ONE proof additionally sharded over all N GPUs (configs[4]); 0 = skip")
+    ap.add_argument("--exchange", default="shm", choices=["shm", "nccl"], help="exchange hook of the sharded proof")
     return ap.parse_args()
 
 
@@ -134,6 +137,83 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_sharded(args, sb, torch, dist, rank, world, local_rank, flush_l2, barrier):
+    """ONE proof of 2^shard_log_size constraints sharded over all ranks: constraint rows / z columns
+    cyclic, commitment rows in blocks, per-round exchange of 96 bytes per rank; every rank gets the same proof bytes.
+    Time = max over ranks of the CUDA-event time around the prove.  Rank 0 then proves the same R1CS alone."""
+    import hashlib
+    import uuid
+    from otti_b200 import comm as sbcomm
+    s = args.shard_log_size
+    n = 1 << s
+    name = ["/sb200-bench-" + uuid.uuid4().hex[:12]]
+    dist.broadcast_object_list(name, src=0)
+    comm = sbcomm.ShmComm(name[0], rank, world) if args.exchange == "shm" else sbcomm.DistComm()
+    inst, vars_, inputs = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED, pinned=True, rank=rank, world=world)
+    gens = sb.NIZKGens.new(n, n, NUM_INPUTS)
+    proof = None
+    for _ in range(args.warmup):
+        proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE, comm=comm)
+    ext = torch.cuda.ExternalStream(inst.stream)
+    inst.upload_witness(gens, vars_)
+
+    def timed(resident, c):
+        nonlocal proof
+        tot, prof = 0.0, None
+        for i in range(args.steps):
+            flush_l2(i)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext)
+            proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE, resident=resident, comm=c)
+            e1.record(ext)
+            e1.synchronize()
+            tot += e0.elapsed_time(e1)
+            prof = sb.NIZK.last_profile()
+        return tot, prof
+
+    res_ms, prof = timed(True, comm)
+    e2e_ms, _ = timed(False, comm)
+    digest = hashlib.sha256(proof.to_bytes()).digest()
+    t = torch.tensor([res_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    digests = [None] * world
+    dist.all_gather_object(digests, digest)
+    comm.close()
+    del inst
+    single_ms = None
+    if rank == 0:  # the same R1CS on one GPU, for the speed-up
+        inst1, v1, i1 = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED, pinned=True)
+        for _ in range(args.warmup):
+            p1 = sb.NIZK.prove(inst1, v1, i1, gens, sb.Transcript.new(LABEL), TAPE)
+        ext1 = torch.cuda.ExternalStream(inst1.stream)
+        inst1.upload_witness(gens, v1)
+        tot = 0.0
+        for i in range(args.steps):
+            flush_l2(i)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(ext1)
+            p1 = sb.NIZK.prove(inst1, v1, i1, gens, sb.Transcript.new(LABEL), TAPE, resident=True)
+            e1.record(ext1)
+            e1.synchronize()
+            tot += e0.elapsed_time(e1)
+        single_ms = tot / args.steps
+        same_as_single = hashlib.sha256(p1.to_bytes()).digest() == digest
+    barrier()
+    if rank != 0:
+        return None
+    ms = float(t[0]) / args.steps
+    return {
+        "workload": "ONE synthetic Spartan R1CS 2^%d sharded over %d GPUs (rows/columns cyclic, commitment rows in blocks)" % (s, world),
+        "scaling": "strong", "prove_ms": ms, "constraints_per_s": n / (ms * 1e-3),
+        "e2e_prove_ms": float(t[1]) / args.steps, "single_gpu_prove_ms": single_ms,
+        "speedup_vs_single_gpu": (single_ms / ms) if single_ms else None,
+        "exchange": args.exchange, "exchange_calls_per_proof": int(prof["exchange_calls"]), "exchange_ms_rank0": 1e3 * prof["exchange"],
+        "phases_ms_rank0": {k: 1e3 * prof[k] for k in ("polycommit", "prove_sc_phase_one", "prove_sc_phase_two", "polyeval")},
+        "proof_identical_on_all_ranks": all(d == digest for d in digests), "proof_identical_to_single_gpu": same_as_single,
+    }
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -142,6 +222,7 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank, world)
 
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line (NCCL prints its version banner there)
     import torch
     import otti_b200 as sb
     if not torch.cuda.is_available():
@@ -208,6 +289,10 @@ def main():
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     res_ms, e2e_ms = float(t[0]), float(t[1])
+
+    sharded = None
+    if dist is not None and args.shard_log_size > 0:
+        sharded = run_sharded(args, sb, torch, dist, rank, world, local_rank, flush_l2, barrier)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -288,6 +373,8 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
     }
+    if sharded is not None:
+        line["sharded"] = sharded
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

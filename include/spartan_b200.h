@@ -188,8 +188,9 @@ int sb200_nizk_verify(const sb200_instance* inst, const uint8_t* inputs32, uint6
  *             witness h2d (inside total), critical-path host Fiat-Shamir time (inside total),
  *             kernel launches, host->device bytes, device->host bytes,
  *             device time of the commitment MSM kernel, device time of the first cubic sum-check kernel
- *             (both from CUDA events on the instance's stream) */
-int sb200_last_prove_profile(double out[12]);
+ *             (both from CUDA events on the instance's stream),
+ *             [12] seconds inside the exchange hook, [13] exchange calls, [14] world, [15] reserved */
+int sb200_last_prove_profile(double out[16]);
 
 /* Measurement helpers (no reference counterpart).
  * sb200_witness_upload places vars in HBM so that a following sb200_nizk_prove(vars32 = NULL, same

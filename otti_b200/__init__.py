@@ -324,8 +324,9 @@ class NIZK:
     @staticmethod
     def last_profile():
         """Timer scopes of the last prove (timer.rs; r1csproof.rs:155-307)."""
-        d = (C.c_double * 12)()
+        d = (C.c_double * 16)()
         lib().sb200_last_prove_profile(d)
         keys = ["polycommit", "prove_sc_phase_one", "prove_sc_phase_two", "polyeval", "total", "h2d", "host_fiat_shamir",
-                "kernel_launches", "h2d_bytes", "d2h_bytes", "msm_commit_kernel", "sc_cubic_round0_kernel"]
+                "kernel_launches", "h2d_bytes", "d2h_bytes", "msm_commit_kernel", "sc_cubic_round0_kernel", "exchange",
+                "exchange_calls", "world", "reserved"]
         return dict(zip(keys, list(d)))

@@ -23,7 +23,7 @@ namespace sbh {
 static thread_local std::string g_err;
 void set_error(const std::string& s) { g_err = s; }
 const char* get_error() { return g_err.c_str(); }
-static thread_local double g_profile[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+static thread_local double g_profile[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 static thread_local uint64_t g_h2d_bytes = 0, g_d2h_bytes = 0;
 
 static bool g_device_ok = false;
@@ -657,8 +657,8 @@ int sb200_comm_selftest_expected(int world, int rounds, uint8_t digest32_out[32]
   return SB200_OK;
 }
 
-int sb200_last_prove_profile(double out[12]) {
-  for (int i = 0; i < 12; i++) out[i] = g_profile[i];
+int sb200_last_prove_profile(double out[16]) {
+  for (int i = 0; i < 16; i++) out[i] = g_profile[i];
   return SB200_OK;
 }
 
