@@ -55,7 +55,8 @@ enum {
   SB200_ERR_NO_DEVICE = -100,
   SB200_ERR_CUDA = -101,
   SB200_ERR_ARG = -102,
-  SB200_ERR_COMM = -103
+  SB200_ERR_COMM = -103,
+  SB200_ERR_ZKIF = -104 /* the reference unwrap()s / panics on such input */
 };
 
 /*
@@ -151,6 +152,27 @@ int sb200_instance_is_sat(const sb200_instance* inst, const uint8_t* vars32, uin
 /* padded sizes: out[0]=num_cons, out[1]=num_vars, out[2]=num_inputs (r1csinstance.rs:124-134) */
 int sb200_instance_dims(const sb200_instance* inst, uint64_t out[3]);
 void sb200_instance_free(sb200_instance* inst);
+
+/*
+ * zkinterface ingestion: R1csReader::new + R1cs::from + R1cs::instance / vars_assignment / inputs_assignment
+ * (spartan-zkinterface/src/lib.rs:75-260, main.rs:36-60).  Host only; parses the three flatbuffers spzk is given
+ * (<circuit.zkif> <inputs.zkif> <witness.zkif>, main.rs:18) into COO triples and canonical assignment bytes.
+ * Variable ids map as in R1cs::translate (lib.rs:96-107): witness position, else input position + num_vars + 1,
+ * else the constant column num_vars; the first occurrence of a duplicated id wins.
+ * SB200_ERR_ZKIF where the reference unwrap()s or panics (wrong message type, missing field, no constraints,
+ * value wider than 32 bytes).
+ *   sb200_r1cs_dims    out = num_cons, num_vars, num_inputs, nnz(A), nnz(B), nnz(C), non_zero_entries (lib.rs:250)
+ *   sb200_r1cs_matrix  m = 0,1,2 -> A,B,C as (rows, cols, 32-byte LE values), owned by the object
+ *   sb200_r1cs_instance == R1cs::instance (Instance::new on the parsed matrices; rank/world as in *_new_sharded) */
+typedef struct sb200_r1cs sb200_r1cs;
+int sb200_zkif_parse(const uint8_t* circuit, size_t circuit_len, const uint8_t* header, size_t header_len, const uint8_t* witness,
+                     size_t witness_len, sb200_r1cs** out);
+int sb200_r1cs_dims(const sb200_r1cs* r, uint64_t out[7]);
+int sb200_r1cs_matrix(const sb200_r1cs* r, int m, const uint64_t** rows, const uint64_t** cols, const uint8_t** vals32);
+const uint8_t* sb200_r1cs_vars(const sb200_r1cs* r);
+const uint8_t* sb200_r1cs_inputs(const sb200_r1cs* r);
+int sb200_r1cs_instance(const sb200_r1cs* r, int rank, int world, sb200_instance** out);
+void sb200_r1cs_free(sb200_r1cs* r);
 
 /* NIZKGens::new(num_cons, num_vars, num_inputs)                          lib.rs:466-477
  * label is b"gens_r1cs_sat" in the reference (lib.rs:475); NULL selects it.

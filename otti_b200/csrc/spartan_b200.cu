@@ -459,6 +459,7 @@ void sb200_gens_free(sb200_gens* h) { delete reinterpret_cast<Gens*>(h); }
 
 // =============================================================================== prover
 #include "host/comm.hpp"
+#include "host/zkif.hpp"
 #include "host/pool.hpp"
 #include "host/tape.hpp"
 #include "prover.inc"
@@ -595,6 +596,49 @@ int sb200_witness_upload(const sb200_instance* hi, const sb200_gens* hg, const u
 uint64_t sb200_instance_stream(const sb200_instance* hi) {
   return hi ? (uint64_t)(uintptr_t) reinterpret_cast<const Instance*>(hi)->ws.stream : 0;
 }
+
+// ---- zkinterface ingestion (spartan-zkinterface/src/lib.rs:75-260); host only ---------------
+struct sb200_r1cs { ZkR1cs r; };
+int sb200_zkif_parse(const uint8_t* circuit, size_t circuit_len, const uint8_t* header, size_t header_len, const uint8_t* witness,
+                     size_t witness_len, sb200_r1cs** out) {
+  if (!circuit || !header || !witness || !out) return SB200_ERR_ARG;
+  *out = nullptr;
+  sb200_r1cs* r = new sb200_r1cs();
+  bool ok = false;
+  try {
+    ok = r->r.parse(circuit, circuit_len, header, header_len, witness, witness_len);
+  } catch (const std::exception& e) {
+    r->r.error = std::string("exception: ") + e.what();
+  }
+  if (!ok) {
+    set_error("zkif: " + r->r.error);
+    delete r;
+    return SB200_ERR_ZKIF;
+  }
+  *out = r;
+  return SB200_OK;
+}
+int sb200_r1cs_dims(const sb200_r1cs* r, uint64_t out[7]) {
+  if (!r || !out) return SB200_ERR_ARG;
+  out[0] = r->r.num_cons; out[1] = r->r.num_vars; out[2] = r->r.num_inputs;
+  for (int m = 0; m < 3; m++) out[3 + m] = r->r.rows[m].size();
+  out[6] = r->r.non_zero_entries;
+  return SB200_OK;
+}
+int sb200_r1cs_matrix(const sb200_r1cs* r, int m, const uint64_t** rows, const uint64_t** cols, const uint8_t** vals32) {
+  if (!r || m < 0 || m > 2 || !rows || !cols || !vals32) return SB200_ERR_ARG;
+  *rows = r->r.rows[m].data(); *cols = r->r.cols[m].data(); *vals32 = r->r.vals[m].data();
+  return SB200_OK;
+}
+const uint8_t* sb200_r1cs_vars(const sb200_r1cs* r) { return r ? r->r.vars.data() : nullptr; }
+const uint8_t* sb200_r1cs_inputs(const sb200_r1cs* r) { return r ? r->r.inputs.data() : nullptr; }
+int sb200_r1cs_instance(const sb200_r1cs* r, int rank, int world, sb200_instance** out) {
+  if (!r || !out) return SB200_ERR_ARG;
+  const uint64_t* rows[3]; const uint64_t* cols[3]; const uint8_t* vals[3]; uint64_t nnz[3];
+  for (int m = 0; m < 3; m++) { rows[m] = r->r.rows[m].data(); cols[m] = r->r.cols[m].data(); vals[m] = r->r.vals[m].data(); nnz[m] = r->r.rows[m].size(); }
+  return sb200_instance_new_sharded(r->r.num_cons, r->r.num_vars, r->r.num_inputs, rows, cols, vals, nnz, rank, world, out);
+}
+void sb200_r1cs_free(sb200_r1cs* r) { delete r; }
 
 // ---- exchange for sharded proofs ------------------------------------------------------------
 int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out) {
