@@ -316,7 +316,7 @@ __device__ __forceinline__ fl_t bind1(const fl_t& lo, const fl_t& hi, const fl_t
 // M = FlInl for the long rounds (the loop body is reused), FlCall for the short ones, where a round is
 // one pass over ~14 multiplications per thread and the kernel must stay inside the instruction cache.
 template <bool BIND, class M>
-__global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
+__global__ void __launch_bounds__(256, 2) sc_cubic_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
                                                        fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
                                                        unsigned int* counter, fl_t* result, Mailbox mb) {
   __shared__ fl_t smem[3 * 32];
@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(256) sc_cubic_kernel(fl_t* __restrict__ T, fl_
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
 template <bool BIND, class M>
-__global__ void __launch_bounds__(256) sc_quad_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
+__global__ void __launch_bounds__(256, 2) sc_quad_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
                                                       fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
   __shared__ fl_t smem[3 * 32];
   const size_t h = newlen >> 1;
@@ -431,12 +431,26 @@ __global__ void bound_partial_kernel(const fl_t* __restrict__ Z, const fl_t* __r
 __global__ void bound_sum_kernel(const fl_t* __restrict__ tmp, uint32_t Rsize, uint32_t jc, fl_t* __restrict__ out) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Rsize) return;
-  fl_t acc = fl_zero();
-  for (uint32_t c = 0; c < jc; c++) acc = fl_add(acc, ld_fl(tmp + (size_t)c * Rsize + i));
-  st_fl(out + i, acc);
+  // four independent partial sums: the loads of a step do not wait for the previous step's addition
+  fl_t acc[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) acc[k] = fl_zero();
+  uint32_t c = 0;
+  for (; c + 4 <= jc; c += 4) {
+    fl_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = ldg_fl(tmp + (size_t)(c + k) * Rsize + i);
+#pragma unroll
+    for (int k = 0; k < 4; k++) acc[k] = fl_add(acc[k], v[k]);
+  }
+  for (; c < jc; c++) acc[0] = fl_add(acc[0], ldg_fl(tmp + (size_t)c * Rsize + i));
+  st_fl(out + i, fl_add(fl_add(acc[0], acc[1]), fl_add(acc[2], acc[3])));
 }
+// chunks of rows: enough blocks for ~8 per SM, but few enough (<= 64) that the second pass stays short
 static inline uint32_t bound_chunks(uint32_t Lsize, uint32_t Rsize) {
-  uint32_t want = (uint32_t)((size_t)kSMs * 1024 / (Rsize ? Rsize : 1));
+  uint32_t xblocks = (Rsize + 127) / 128;
+  uint32_t want = (uint32_t)(8 * kSMs + xblocks - 1) / xblocks;
+  if (want > 64) want = 64;
   if (want < 1) want = 1;
   if (want > Lsize) want = Lsize;
   return want;
@@ -781,7 +795,8 @@ __device__ __forceinline__ ge_t warp_sum_ge(ge_t x) {
   }
   return x;
 }
-// valid in thread 0; smem: ge_t[blockDim.x / 32]
+// valid in thread 0; smem: ge_t[blockDim.x / 32].  The second level only runs the shuffle steps that can
+// still carry data (log2 of the number of warps): every skipped step is a full point addition of latency.
 __device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
   x = warp_sum_ge(x);
@@ -790,9 +805,23 @@ __device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {
   __syncthreads();
   if (wid == 0) {
     x = lane < nw ? smem[lane] : ge_identity();
-    x = warp_sum_ge(x);
+    int first = 16;
+    while (first >= nw && first > 0) first >>= 1;
+    x = warp_sum_ge_from(x, first);
   }
   return x;
+}
+// sum of `count` <= blockDim.x values, one per thread (identity elsewhere); valid in thread 0
+__device__ __forceinline__ ge_t block_sum_ge_n(ge_t x, uint32_t count, ge_t* smem) {
+  if (count <= 32) {  // all of them sit in warp 0
+    if (threadIdx.x < 32) {
+      int first = 16;
+      while (first >= (int)count && first > 0) first >>= 1;
+      x = warp_sum_ge_from(x, first);
+    }
+    return x;
+  }
+  return block_sum_ge(x, smem);
 }
 __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows,
                                                         const fl_t* __restrict__ scalars, size_t stride, uint32_t n,
@@ -839,9 +868,9 @@ __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restric
       uint4 v = __ldcg(src + i);
       tw[4 * i] = v.x; tw[4 * i + 1] = v.y; tw[4 * i + 2] = v.z; tw[4 * i + 3] = v.w;
     }
-    acc = ge_add_call(acc, tmp);
+    acc = b < blockDim.x && b == threadIdx.x ? tmp : ge_add_call(acc, tmp);
   }
-  acc = block_sum_ge(acc, smem);
+  acc = block_sum_ge_n(acc, gridDim.x, smem);
   if (threadIdx.x == 0) {
     out[row] = acc;
     counters[row] = 0;
