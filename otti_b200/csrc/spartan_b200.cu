@@ -427,10 +427,10 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
   }
   // Window width of the device tables: every extra bit removes madds from the commitment kernel
   // (floor(252/c)+1 per term) and doubles the table.  Largest c whose table fits SB200_TABLE_MB
-  // (default 20 GiB of the 180 GB HBM); SB200_MSM_WINDOW forces a value.
+  // (default 64 GiB of the 180 GB HBM: c = 16/16/15/14 at 2^16/2^20/2^22/2^24); SB200_MSM_WINDOW forces a value.
   uint32_t c = 8;
   {
-    size_t budget = (size_t)20480 << 20;
+    size_t budget = (size_t)65536 << 20;
     if (const char* env = getenv("SB200_TABLE_MB")) {
       long v = atol(env);
       if (v > 0) budget = (size_t)v << 20;
