@@ -49,6 +49,9 @@ size_t msm_small_scratch_bytes(uint32_t rows, uint32_t n, uint32_t windows);
 // first element of up to four device vectors -> host mailbox (mapped memory), then *host_flag = seq
 cudaError_t k_mail(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
                    uint32_t seq, cudaStream_t s);
+// first `count` entries of ntab <= 4 tables -> host mailbox (table k at host + k*count), then *host_flag = seq
+cudaError_t k_mail_tables(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int ntab, uint32_t count, fl_t* host,
+                          uint32_t* host_flag, uint32_t seq, cudaStream_t s);
 
 // ---- F_l vector kernels -------------------------------------------------------------------
 // canonical -> Montgomery, flag[0] |= 1 if any input >= l            (lib.rs:65-89)

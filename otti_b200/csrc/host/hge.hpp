@@ -326,6 +326,11 @@ struct FixedBase {
     for (int w = 0; w < 32; w++)
       if (k[w]) acc = ge_madd(acc, tbl[w * 255 + k[w] - 1]);
   }
+  // windows [w0, w1) only: k*P is a sum over windows, so one multiplication can be split over threads
+  void mul_acc_range(Ge& acc, const uint8_t k[32], int w0, int w1) const {
+    for (int w = w0; w < w1; w++)
+      if (k[w]) acc = ge_madd(acc, tbl[w * 255 + k[w] - 1]);
+  }
 };
 
 }  // namespace sbh

@@ -75,6 +75,7 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   uint8_t* mail_dev = nullptr;  // the same memory as seen from the device
   uint32_t seq = 0;             // mailbox sequence number, never reused
   cudaStream_t stream = nullptr;
+  int device = 0;  // the CUDA device of this workspace (helper threads must select it before launching)
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // [0,1] commit MSM kernel, [2,3] first cubic round
   ~Workspace() {
     for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);

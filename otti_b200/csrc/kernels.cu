@@ -386,6 +386,131 @@ __global__ void __launch_bounds__(256, 2) sc_quad_kernel(fl_t* __restrict__ Z, f
   }
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
+// ---- latency variants for the short rounds --------------------------------------------------
+// A short round is one pass of ~14 dependent field multiplications per thread in the kernels above: ~25 us however
+// little data there is.  Here FOUR threads share a pair: each binds one table (cubic) or one table half (quadratic),
+// the bound values meet in shared memory, and three (two) of the four threads evaluate one point each -- the
+// dependent chain shrinks to 3-4 multiplications.  Lane l works on value index l & 3, so sums over equal indices
+// are shuffles by 16, 8, 4.
+__device__ __forceinline__ fl_t shfl_down_fl(const fl_t& x, int o) {
+  fl_t y;
+#pragma unroll
+  for (int i = 0; i < 8; i++) y.v[i] = __shfl_down_sync(0xffffffffu, x.v[i], o);
+  return y;
+}
+// e: this thread's term of value index (threadIdx.x & 3); sums over the grid end up in result[0..3) (index 3 unused)
+__device__ __forceinline__ void quad_grid_sum(fl_t e, fl_t (*sred)[4], fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
+  __shared__ bool s_last_q;
+  const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll 1
+  for (int o = 16; o >= 4; o >>= 1) e = fl_add(e, shfl_down_fl(e, o));
+  if (lane < 4) sred[wid][lane] = e;
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    fl_t acc = sred[0][threadIdx.x];
+    for (uint32_t w = 1; w < nw; w++) acc = fl_add(acc, sred[w][threadIdx.x]);
+    st_fl(&partials[(size_t)blockIdx.x * 4 + threadIdx.x], acc);
+    __threadfence();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int t = atomicAdd(counter, 1u);
+    s_last_q = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last_q) return;
+  __threadfence();
+  fl_t acc = fl_zero();
+  for (uint32_t b = threadIdx.x >> 2; b < gridDim.x; b += blockDim.x >> 2) acc = fl_add(acc, ldcg_fl(&partials[(size_t)b * 4 + (threadIdx.x & 3)]));
+#pragma unroll 1
+  for (int o = 16; o >= 4; o >>= 1) acc = fl_add(acc, shfl_down_fl(acc, o));
+  __syncthreads();
+  if (lane < 4) sred[wid][lane] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    if (threadIdx.x < 3) {
+      fl_t tot = sred[0][threadIdx.x];
+      for (uint32_t w = 1; w < nw; w++) tot = fl_add(tot, sred[w][threadIdx.x]);
+      st_fl(&result[threadIdx.x], tot);
+      if (mb.host_flag != nullptr) {
+        st_fl(&mb.host_result[threadIdx.x], tot);
+        __threadfence_system();
+      }
+    }
+    __syncwarp();
+    if (threadIdx.x == 0) {
+      *counter = 0;
+      if (mb.host_flag != nullptr) {
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(mb.host_flag) = mb.seq;
+      }
+    }
+  }
+}
+template <bool BIND>
+__global__ void __launch_bounds__(256) sc_cubic_lat_kernel(fl_t* __restrict__ T, fl_t* __restrict__ A, fl_t* __restrict__ B,
+                                                           fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
+                                                           unsigned int* counter, fl_t* result, Mailbox mb) {
+  __shared__ fl_t sv[64][3][4];  // [pair of the block][point 0,2,3][table]
+  __shared__ fl_t sred[8][4];
+  const size_t h = newlen >> 1;
+  const uint32_t k = threadIdx.x & 3, pl = threadIdx.x >> 2;
+  const size_t pair = (size_t)blockIdx.x * 64 + pl;
+  fl_t* X = k == 0 ? T : k == 1 ? A : k == 2 ? B : C;
+  fl_t lo = fl_zero(), hi = fl_zero();
+  if (pair < h) {
+    if (BIND) {
+      fl_t a0 = ld_fl(X + pair), a1 = ld_fl(X + pair + newlen), b0 = ld_fl(X + pair + h), b1 = ld_fl(X + pair + h + newlen);
+      lo = bind1<FlInl>(a0, a1, r);
+      hi = bind1<FlInl>(b0, b1, r);
+      st_fl(X + pair, lo);
+      st_fl(X + pair + h, hi);
+    } else {
+      lo = ld_fl(X + pair);
+      hi = ld_fl(X + pair + h);
+    }
+  }
+  if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 4) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
+  const fl_t d = fl_sub(hi, lo), p2 = fl_add(hi, d), p3 = fl_add(p2, d);  // values at 0, 2, 3 of this table's line
+  sv[pl][0][k] = lo;
+  sv[pl][1][k] = p2;
+  sv[pl][2][k] = p3;
+  __syncthreads();
+  fl_t e = fl_zero();
+  if (k < 3 && pair < h)  // comb(T,A,B,C) = T*(A*B - C) at point k (sumcheck.rs:622-650, r1csproof.rs:84-88)
+    e = fl_mul(sv[pl][k][0], fl_sub(fl_mul(sv[pl][k][1], sv[pl][k][2]), sv[pl][k][3]));
+  quad_grid_sum(e, sred, partials, counter, result, mb);
+}
+template <bool BIND>
+__global__ void __launch_bounds__(256) sc_quad_lat_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t newlen, fl_t r,
+                                                          fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
+  __shared__ fl_t sv[64][4];  // [pair of the block][zl, ql, zh, qh]
+  __shared__ fl_t sred[8][4];
+  const size_t h = newlen >> 1;
+  const uint32_t k = threadIdx.x & 3, pl = threadIdx.x >> 2;
+  const size_t pair = (size_t)blockIdx.x * 64 + pl;
+  fl_t* X = (k & 1) ? Q : Z;
+  const size_t at = pair + ((k & 2) ? h : 0);
+  fl_t v = fl_zero();
+  if (pair < h) {
+    if (BIND) {
+      v = bind1<FlInl>(ld_fl(X + at), ld_fl(X + at + newlen), r);
+      st_fl(X + at, v);
+    } else {
+      v = ld_fl(X + at);
+    }
+  }
+  if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 2) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
+  sv[pl][k] = v;
+  __syncthreads();
+  fl_t e = fl_zero();
+  if (pair < h) {  // sumcheck.rs:459-467
+    if (k == 0) e = fl_mul(sv[pl][0], sv[pl][1]);
+    else if (k == 1) e = fl_mul(fl_sub(fl_add(sv[pl][2], sv[pl][2]), sv[pl][0]), fl_sub(fl_add(sv[pl][3], sv[pl][3]), sv[pl][1]));
+  }
+  quad_grid_sum(e, sred, partials, counter, result, mb);
+}
+static constexpr size_t kLatPairs = 8192;  // rounds with at most this many pairs run the latency variants
 static constexpr unsigned kCompactBlocks = 148;  // rounds with at most one block per SM run the compact kernels
 static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
   size_t g = (pairs + 255) / 256;
@@ -398,6 +523,13 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
+  if (newlen / 2 <= kLatPairs && w.max_blocks >= kLatPairs / 64) {
+    unsigned gl = (unsigned)((newlen / 2 + 63) / 64);
+    if (gl < 1) gl = 1;
+    if (do_bind) sc_cubic_lat_kernel<true><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+    else sc_cubic_lat_kernel<false><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+    return SB_LAUNCHED();
+  }
   const bool compact = g <= kCompactBlocks;
   if (do_bind && compact) sc_cubic_kernel<true, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
   else if (do_bind) sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
@@ -409,6 +541,13 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
+  if (newlen / 2 <= kLatPairs && w.max_blocks >= kLatPairs / 64) {
+    unsigned gl = (unsigned)((newlen / 2 + 63) / 64);
+    if (gl < 1) gl = 1;
+    if (do_bind) sc_quad_lat_kernel<true><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+    else sc_quad_lat_kernel<false><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+    return SB_LAUNCHED();
+  }
   const bool compact = g <= kCompactBlocks;
   if (do_bind && compact) sc_quad_kernel<true, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
   else if (do_bind) sc_quad_kernel<true, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
@@ -917,6 +1056,23 @@ __global__ void mail_kernel(const fl_t* p0, const fl_t* p1, const fl_t* p2, cons
 cudaError_t k_mail(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
                    uint32_t seq, cudaStream_t s) {
   mail_kernel<<<1, 32, 0, s>>>(p0, p1, p2, p3, n, host, host_flag, seq);
+  return SB_LAUNCHED();
+}
+// the first `count` entries of up to four tables to a host mailbox (table k at host + k*count), then the flag
+__global__ void mail_tables_kernel(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int ntab, uint32_t count,
+                                   fl_t* host, uint32_t* host_flag, uint32_t seq) {
+  const fl_t* src[4] = {p0, p1, p2, p3};
+  for (uint32_t i = threadIdx.x; i < (uint32_t)ntab * count; i += blockDim.x) st_fl(host + i, ld_fl(src[i / count] + (i % count)));
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    *reinterpret_cast<volatile uint32_t*>(host_flag) = seq;
+  }
+}
+cudaError_t k_mail_tables(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int ntab, uint32_t count, fl_t* host,
+                          uint32_t* host_flag, uint32_t seq, cudaStream_t s) {
+  mail_tables_kernel<<<1, 256, 0, s>>>(p0, p1, p2, p3, ntab, count, host, host_flag, seq);
   return SB_LAUNCHED();
 }
 

@@ -6,6 +6,7 @@
 // Spartan/src/lib.rs:493-535 and r1csproof.rs:141-345 statement by statement
 // (transcript framing SURVEY.md App. A.1, tape draw order App. A.2).
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -24,7 +25,7 @@ static thread_local std::string g_err;
 void set_error(const std::string& s) { g_err = s; }
 const char* get_error() { return g_err.c_str(); }
 static thread_local double g_profile[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-static thread_local uint64_t g_h2d_bytes = 0, g_d2h_bytes = 0;
+static std::atomic<uint64_t> g_h2d_bytes{0}, g_d2h_bytes{0};  // one proof at a time per process (prove_mu); counted from two threads
 
 static bool g_device_ok = false;
 static int ensure_device() {

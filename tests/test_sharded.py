@@ -72,11 +72,13 @@ def test_torch_distributed_exchange_gloo_world2():
         assert got == want and calls == 12
 
 
-def _run_sharded(world, case, tmp_path):
+def _run_sharded(world, case, tmp_path, env=None):
     name = "/sb200-g-" + uuid.uuid4().hex[:12]
     out = str(tmp_path / "proof")
+    e = dict(os.environ)
+    e.update(env or {})
     ps = [subprocess.Popen([sys.executable, os.path.join(HERE, "shard_worker.py"), str(r), str(world), name, "0", case, out],
-                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT) for r in range(world)]
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, env=e) for r in range(world)]
     logs = [p.communicate(timeout=600)[0].decode() for p in ps]
     assert all(p.returncode == 0 for p in ps), "\n".join(logs)
     return [open("%s.%d" % (out, r), "rb").read() for r in range(world)]
@@ -115,3 +117,17 @@ def test_sharded_too_small_is_refused(tmp_path):
     p = subprocess.run([sys.executable, os.path.join(HERE, "shard_worker.py"), "0", "8", name, "0", "syn:2", str(tmp_path / "x")],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=300)
     assert p.returncode != 0 and b"too small" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,tail,s", [(1, 0, 9), (1, 3, 9), (1, 8, 9), (1, 8, 5), (2, 0, 9), (2, 8, 9), (4, 5, 12), (1, 6, 2)])
+def test_host_tail_rounds_do_not_change_the_proof(world, tail, s, tmp_path):
+    """The last SB200_HOST_TAIL_LOG rounds of each sum-check run on the host over the short tables (prover.inc);
+    whatever the split between device and host rounds, the proof bytes are the oracle's."""
+    n = 1 << s
+    ni = min(10, n - 1)
+    oi, ov, oin = O.Instance.synthetic(n, n, ni, 0x0771)
+    og = O.Gens(n, n, ni)
+    want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED)
+    for r in _run_sharded(world, "syn:%d" % s, tmp_path, {"SB200_HOST_TAIL_LOG": str(tail)}):
+        assert r[16:] == want
