@@ -89,7 +89,7 @@ class HostPool {
         if (ranks > 1) hw /= ranks;
       }
       int n = hw > 2 ? hw - 2 : (hw == 2 ? 1 : 0);  // with two cores: this thread + the tape drawer
-      if (n > 7) n = 7;
+      if (n > 10) n = 10;
       if (const char* e = getenv("SB200_HOST_THREADS")) n = atoi(e);
       if (n < 0) n = 0;
       if (n > 32) n = 32;
