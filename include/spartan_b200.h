@@ -174,6 +174,36 @@ const uint8_t* sb200_r1cs_inputs(const sb200_r1cs* r);
 int sb200_r1cs_instance(const sb200_r1cs* r, int rank, int world, sb200_instance** out);
 void sb200_r1cs_free(sb200_r1cs* r);
 
+/*
+ * rust-circ adapter: r1cs_to_spartan + lc_to_v + int_to_scalar        rust-circ/src/target/r1cs/spartan.rs:31-186
+ * A CirC `R1cs` (signals by name, linear combinations over arbitrary-precision integers) -> the same sb200_r1cs
+ * object the zkinterface reader returns, so the SGD pipeline (rust-circ/examples/circ.rs:246-273) can hand its circuit
+ * over in memory.  Host only.
+ *   signals      r1cs.values in the caller's iteration order (the reference iterates a HashMap, i.e. in no defined
+ *                order): CirC id, name (names[name_off[s] .. name_off[s+1])) and value.  A name containing
+ *                "main_f0_lex0_w" is a witness, else one containing "main_f0_lex0_" an input, else a witness
+ *                (spartan.rs:52-75); witnesses / inputs are numbered in the order they are met.
+ *   integers     little-endian MAGNITUDE bytes of any length: integer k of a list is bytes[off[k] .. off[k+1]).
+ *                int_to_scalar reads rug's limbs, which carry no sign (spartan.rs:141-160): value = |i| mod l.
+ *   n_public     r1cs.public_idxs.len(), which the reference asserts to be 0 (spartan.rs:42)
+ *   next_idx     r1cs.next_idx; the reference asserts wit.len() + inp.len() == next_idx (spartan.rs:80)
+ *   constraints  for m = 0,1,2 (A,B,C): monomials of constraint i are [lc_off[m][i], lc_off[m][i+1]) of
+ *                mono_ids[m] / coeff_*[m] (caller's order); const_*[m] holds lc.constant of every constraint,
+ *                added on the constant column num_vars when non-zero (spartan.rs:177-184).
+ * Column mapping (spartan.rs:96-99,168-175): witness position, input position + num_vars + 1.
+ * SB200_ERR_ASSERT where the reference asserts, unwrap()s or panics (public inputs present, next_idx mismatch,
+ * monomial id >= num_vars "variable number off", unknown id).
+ * Continue with sb200_r1cs_instance / sb200_r1cs_vars / sb200_r1cs_inputs; the reference then asserts
+ * Instance::is_sat (spartan.rs:135-136), which is sb200_instance_is_sat.
+ */
+int sb200_circ_r1cs(uint64_t n_signals, const uint64_t* signal_ids, const uint8_t* names, const uint64_t* name_off,
+                    const uint8_t* value_bytes, const uint64_t* value_off, uint64_t n_public, uint64_t next_idx, uint64_t n_cons,
+                    const uint64_t* const lc_off[3], const uint64_t* const mono_ids[3], const uint8_t* const coeff_bytes[3],
+                    const uint64_t* const coeff_off[3], const uint8_t* const const_bytes[3], const uint64_t* const const_off[3],
+                    sb200_r1cs** out);
+/* int_to_scalar (spartan.rs:141-160) on one integer: |i| mod l as 32 canonical little-endian bytes */
+int sb200_circ_int_to_scalar(const uint8_t* magnitude_le, size_t len, uint8_t out32[32]);
+
 /* NIZKGens::new(num_cons, num_vars, num_inputs)                          lib.rs:466-477
  * label is b"gens_r1cs_sat" in the reference (lib.rs:475); NULL selects it.
  * Besides deriving the generators this builds the fixed-base window tables in

@@ -36,6 +36,9 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
 // Two-step form: row sums without any blind term, then (partials + extra_h[row]*base[h_index]) -> compressed.
 cudaError_t msm_fixed_rows(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t rows, uint32_t n, void* scratch,
                            cudaStream_t s, cudaEvent_t* ev = nullptr);
+// rows [row0, row0 + nrows) of a total_rows-row job (same plan and scratch layout as msm_fixed_rows over all rows)
+cudaError_t msm_fixed_rows_part(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t total_rows, uint32_t row0,
+                                uint32_t nrows, uint32_t n, void* scratch, cudaStream_t s);
 cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const fl_t* extra_h, uint32_t h_index,
                              const void* scratch, uint8_t* out32, cudaStream_t s);
 size_t msm_scratch_bytes(uint32_t rows, uint32_t n);

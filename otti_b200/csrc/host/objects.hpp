@@ -77,8 +77,19 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   cudaStream_t stream = nullptr;
   int device = 0;  // the CUDA device of this workspace (helper threads must select it before launching)
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // [0,1] commit MSM kernel, [2,3] first cubic round
+  // pipelined witness upload (prover.inc): pieces are copied on copy_stream and committed on msm_stream[0/1]
+  static constexpr int kMaxPieces = 8;
+  cudaStream_t copy_stream = nullptr, msm_stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev_piece[kMaxPieces] = {}, ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
   ~Workspace() {
     for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);
+    for (int i = 0; i < kMaxPieces; i++) if (ev_piece[i]) cudaEventDestroy(ev_piece[i]);
+    if (ev_fork) cudaEventDestroy(ev_fork);
+    for (int i = 0; i < 2; i++) {
+      if (ev_join[i]) cudaEventDestroy(ev_join[i]);
+      if (msm_stream[i]) cudaStreamDestroy(msm_stream[i]);
+    }
+    if (copy_stream) cudaStreamDestroy(copy_stream);
     if (pinned) cudaFreeHost(pinned);
     if (blind_stage) cudaFreeHost(blind_stage);
     if (mail) cudaFreeHost(mail);

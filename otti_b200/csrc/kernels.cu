@@ -748,6 +748,67 @@ __device__ __forceinline__ ge_t warp_sum_ge_from(ge_t x, int first_offset) {
   for (int o = first_offset; o > 0; o >>= 1) x = ge_add_call(x, shfl_down_ge(x, o));
   return x;
 }
+// ---- point sums with four lanes per addition
+// A tree level of a point sum leaves most lanes idle, and a lone warp pays the full latency of the nine dependent
+// field multiplications of an addition.  Here the four lanes of a quad (lanes 4g..4g+3) hold the same P and Q and
+// share one addition: each lane computes one of the four products of either half of add-2008-hwcd-3, the halves meet
+// through shuffles -- three multiplications deep instead of nine.  Every lane of the warp must call.
+__device__ __forceinline__ fp_t shfl_fp(const fp_t& x, int src) {
+  fp_t y;
+#pragma unroll
+  for (int i = 0; i < 8; i++) y.v[i] = __shfl_sync(0xffffffffu, x.v[i], src);
+  return y;
+}
+__device__ __forceinline__ ge_t shfl_ge(const ge_t& x, int src) {
+  ge_t y;
+  y.X = shfl_fp(x.X, src); y.Y = shfl_fp(x.Y, src); y.Z = shfl_fp(x.Z, src); y.T = shfl_fp(x.T, src);
+  return y;
+}
+__device__ __forceinline__ fp_t fp_sel(bool c, const fp_t& a, const fp_t& b) {
+  fp_t r;
+#pragma unroll
+  for (int i = 0; i < 8; i++) r.v[i] = c ? a.v[i] : b.v[i];
+  return r;
+}
+static __device__ __noinline__ ge_t ge_add_quad(ge_t p, ge_t q) {
+  const int lane = threadIdx.x & 31, role = lane & 3, base = lane & ~3;
+  // first half: role 0: A = (Y1-X1)(Y2-X2), 1: B = (Y1+X1)(Y2+X2), 2: D = 2 Z1 Z2, 3: C = 2d T1 T2
+  fp_t a = role == 0 ? fp_sub(p.Y, p.X) : role == 1 ? fp_add(p.Y, p.X) : role == 2 ? p.Z : p.T;
+  fp_t b = role == 0 ? fp_sub(q.Y, q.X) : role == 1 ? fp_add(q.Y, q.X) : role == 2 ? q.Z : q.T;
+  fp_t m = fp_mul_call(a, b);
+  m = fp_mul_call(m, fp_sel(role == 3, fp_2d(), fp_one()));
+  m = fp_sel(role == 2, fp_add(m, m), m);
+  const fp_t A = shfl_fp(m, base), B = shfl_fp(m, base + 1), D = shfl_fp(m, base + 2), C = shfl_fp(m, base + 3);
+  const fp_t E = fp_sub(B, A), Fv = fp_sub(D, C), G = fp_add(D, C), H = fp_add(B, A);
+  // second half: role 0: X = E F, 1: Y = G H, 2: Z = F G, 3: T = E H
+  a = fp_sel((role & 1) == 0, fp_sel(role == 0, E, Fv), fp_sel(role == 1, G, E));
+  b = fp_sel((role & 1) == 0, fp_sel(role == 0, Fv, G), H);
+  m = fp_mul_call(a, b);
+  ge_t r;
+  r.X = shfl_fp(m, base); r.Y = shfl_fp(m, base + 1); r.Z = shfl_fp(m, base + 2); r.T = shfl_fp(m, base + 3);
+  return r;
+}
+// Sum of the values held by lanes [0, count) of a warp (the other lanes must hold the identity); valid in lane 0
+// (in every lane of quad 0).  Every lane of the warp must call, with the same count.
+__device__ __forceinline__ ge_t warp_sum_ge_n(const ge_t& x, uint32_t count) {
+  const int g = (threadIdx.x & 31) >> 2;
+  ge_t y;
+  if (count > 16) {  // 32 -> 16 in two passes of eight additions, then each quad adds its own two sums
+    ge_t r0 = ge_add_quad(shfl_ge(x, g), shfl_ge(x, g + 16));
+    y = ge_add_quad(shfl_ge(x, g + 8), shfl_ge(x, g + 24));
+    y = ge_add_quad(r0, y);
+  } else if (count > 8) {
+    y = ge_add_quad(shfl_ge(x, g), shfl_ge(x, g + 8));
+  } else {
+    y = shfl_ge(x, g);
+  }
+  // quads [0, min(count, 8)) hold one value each; the levels that could only add identities are skipped
+  const uint32_t q = count < 8 ? count : 8;
+#pragma unroll 1
+  for (int o = 16; o >= 4; o >>= 1)
+    if ((uint32_t)(o >> 2) < q) y = ge_add_quad(y, shfl_down_ge(y, o));
+  return y;
+}
 __device__ __forceinline__ niels_t ldg_niels_signed(const niels_t* p, bool neg) {  // -P = (y-x, y+x, -2dxy)
   niels_t e = ldg_niels(p);
   if (neg) {
@@ -809,35 +870,36 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
         acc = ge_madd(acc, ldg_niels_signed(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(d < 0 ? -d : d) - 1), d < 0), false);
     }
   }
-  acc = warp_sum_ge_from(acc, 16);
+  acc = warp_sum_ge_n(acc, 32);
   if (nw > 1) {
     if (lane == 0) sm[wid] = acc;
     __syncthreads();
     if (wid != 0) return;
     acc = lane < nw ? sm[lane] : ge_identity();
-    acc = warp_sum_ge_from(acc, 4);
+    acc = warp_sum_ge_n(acc, nw);
   }
   if (threadIdx.x == 0) partial[(size_t)row * nsplit + split] = acc;
 }
 // Sums the per-split partials of a row, optionally adds the row's blind*h term (one table look-up per window --
 // kept out of the row kernel so that the commitment can start before the RandomTape has produced the blinds),
-// and compresses.
-__global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit, uint8_t* __restrict__ out32,
-                                  const niels_t* __restrict__ tbl, uint32_t c, uint32_t windows, const fl_t* __restrict__ extra_h,
-                                  uint32_t h_index) {
-  uint32_t row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= rows) return;
-  ge_t acc = partial[(size_t)row * nsplit];
-  for (uint32_t s = 1; s < nsplit; s++) acc = ge_add_call(acc, partial[(size_t)row * nsplit + s]);
-  if (extra_h != nullptr) {
+// and compresses.  One warp per row: the windows of blind*h and the partials are spread over the lanes and summed
+// by the quad tree, so the chain in front of the compression is ~25 field multiplications instead of 7 per window.
+static constexpr int kFinishWarps = 4;
+__global__ void __launch_bounds__(32 * kFinishWarps) msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit,
+                                                                      uint8_t* __restrict__ out32, const niels_t* __restrict__ tbl, uint32_t c,
+                                                                      uint32_t windows, const fl_t* __restrict__ extra_h, uint32_t h_index) {
+  const uint32_t lane = threadIdx.x & 31, row = blockIdx.x * kFinishWarps + (threadIdx.x >> 5);
+  if (row >= rows) return;  // whole warps
+  const uint32_t nh = extra_h != nullptr ? windows : 0, items = nh + nsplit;
+  ge_t acc = ge_identity();
+  if (lane < nh) {
     const size_t epb = (size_t)windows << (c - 1);
     uint32_t kw[8];
     const uint4* q = reinterpret_cast<const uint4*>(extra_h + row);
     uint4 a = __ldg(q), b = __ldg(q + 1);
     kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
-    uint32_t carry = 0;
-    for (uint32_t w = 0; w < windows; w++) {
-      int32_t d = msm_digit(kw, w, c, carry);
+    for (uint32_t w = lane; w < nh; w += 32) {
+      int32_t d = msm_digit_at(kw, w, c);
       if (d != 0) {
         bool neg = d < 0;
         niels_t e = ldg_niels(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(neg ? -d : d) - 1));
@@ -845,11 +907,16 @@ __global__ void msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t row
       }
     }
   }
+  // item i (windows first, then the partials) belongs to lane i mod 32
+  for (uint32_t i = nh + ((lane + 32 - (nh & 31)) & 31); i < items; i += 32) acc = ge_add_call(acc, partial[(size_t)row * nsplit + (i - nh)]);
+  acc = warp_sum_ge_n(acc, items < 32 ? items : 32);
   uint32_t w[8];
   ge_compress_t<FpCall>(acc, w);
-  uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
-  o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-  o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  if (lane == 0) {
+    uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
+    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  }
 }
 MsmPlan msm_plan(uint32_t rows, uint32_t n) {
   MsmPlan p;
@@ -885,8 +952,8 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
-  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c,
-                                                    t.windows, nullptr, 0);
+  msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
+      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, nullptr, 0);
   return SB_LAUNCHED();
 }
 // The same in two halves: the row sums first (no blinds needed), then blind*h + compression.
@@ -902,12 +969,23 @@ cudaError_t msm_fixed_rows(const MsmTable& t, const fl_t* scalars, size_t stride
   if (ev) cudaEventRecord(ev[1], s);
   return e;
 }
+// Rows [row0, row0 + nrows) of a `total_rows`-row job, with the launch plan and the scratch layout of the whole job:
+// the witness can then be committed in pieces, each launched when its part of the host->device copy has landed.
+cudaError_t msm_fixed_rows_part(const MsmTable& t, const fl_t* scalars, size_t stride, uint32_t total_rows, uint32_t row0,
+                                uint32_t nrows, uint32_t n, void* scratch, cudaStream_t s) {
+  if (!nrows) return cudaSuccess;
+  MsmPlan p = msm_plan(total_rows, n);
+  dim3 grid(p.splits, nrows);
+  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars + (size_t)row0 * stride, stride, n, nullptr, 0, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch) + (size_t)row0 * p.splits);
+  return SB_LAUNCHED();
+}
 cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const fl_t* extra_h, uint32_t h_index, const void* scratch,
                              uint8_t* out32, cudaStream_t s) {
   if (!rows) return cudaSuccess;
   MsmPlan p = msm_plan(rows, n);
-  msm_finish_kernel<<<(rows + 31) / 32, 32, 0, s>>>(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c,
-                                                    t.windows, extra_h, h_index);
+  msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
+      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, extra_h, h_index);
   return SB_LAUNCHED();
 }
 
@@ -938,26 +1016,20 @@ __device__ __forceinline__ ge_t warp_sum_ge(ge_t x) {
 // still carry data (log2 of the number of warps): every skipped step is a full point addition of latency.
 __device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
-  x = warp_sum_ge(x);
+  x = warp_sum_ge_n(x, 32);
   __syncthreads();
   if (lane == 0) smem[wid] = x;
   __syncthreads();
   if (wid == 0) {
     x = lane < nw ? smem[lane] : ge_identity();
-    int first = 16;
-    while (first >= nw && first > 0) first >>= 1;
-    x = warp_sum_ge_from(x, first);
+    x = warp_sum_ge_n(x, (uint32_t)nw);
   }
   return x;
 }
 // sum of `count` <= blockDim.x values, one per thread (identity elsewhere); valid in thread 0
 __device__ __forceinline__ ge_t block_sum_ge_n(ge_t x, uint32_t count, ge_t* smem) {
   if (count <= 32) {  // all of them sit in warp 0
-    if (threadIdx.x < 32) {
-      int first = 16;
-      while (first >= (int)count && first > 0) first >>= 1;
-      x = warp_sum_ge_from(x, first);
-    }
+    if (threadIdx.x < 32) x = warp_sum_ge_n(x, count);
     return x;
   }
   return block_sum_ge(x, smem);

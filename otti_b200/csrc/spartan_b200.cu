@@ -461,6 +461,7 @@ void sb200_gens_free(sb200_gens* h) { delete reinterpret_cast<Gens*>(h); }
 // =============================================================================== prover
 #include "host/comm.hpp"
 #include "host/zkif.hpp"
+#include "host/circ.hpp"
 #include "host/pool.hpp"
 #include "host/tape.hpp"
 #include "prover.inc"
@@ -640,6 +641,43 @@ int sb200_r1cs_instance(const sb200_r1cs* r, int rank, int world, sb200_instance
   return sb200_instance_new_sharded(r->r.num_cons, r->r.num_vars, r->r.num_inputs, rows, cols, vals, nnz, rank, world, out);
 }
 void sb200_r1cs_free(sb200_r1cs* r) { delete r; }
+
+// ---- rust-circ adapter (rust-circ/src/target/r1cs/spartan.rs:31-186); host only -------------
+int sb200_circ_r1cs(uint64_t n_signals, const uint64_t* signal_ids, const uint8_t* names, const uint64_t* name_off,
+                    const uint8_t* value_bytes, const uint64_t* value_off, uint64_t n_public, uint64_t next_idx, uint64_t n_cons,
+                    const uint64_t* const lc_off[3], const uint64_t* const mono_ids[3], const uint8_t* const coeff_bytes[3],
+                    const uint64_t* const coeff_off[3], const uint8_t* const const_bytes[3], const uint64_t* const const_off[3],
+                    sb200_r1cs** out) {
+  if (!out || !name_off || !value_off || !lc_off || !mono_ids || !coeff_off || !const_off) return SB200_ERR_ARG;
+  if (n_signals && (!signal_ids || !names || !value_bytes)) return SB200_ERR_ARG;
+  *out = nullptr;
+  CircLcs lcs[3];
+  for (int m = 0; m < 3; m++) {
+    if (!lc_off[m] || !coeff_off[m] || !const_off[m]) return SB200_ERR_ARG;
+    lcs[m] = CircLcs{lc_off[m], mono_ids[m], CircBigInts{coeff_bytes ? coeff_bytes[m] : nullptr, coeff_off[m]},
+                     CircBigInts{const_bytes ? const_bytes[m] : nullptr, const_off[m]}};
+  }
+  sb200_r1cs* r = new sb200_r1cs();
+  bool ok = false;
+  try {
+    ok = circ_r1cs_to_spartan(n_signals, signal_ids, names, name_off, CircBigInts{value_bytes, value_off}, n_public, next_idx, n_cons,
+                              lcs, r->r);
+  } catch (const std::exception& e) {
+    r->r.error = std::string("exception: ") + e.what();
+  }
+  if (!ok) {
+    set_error("circ: " + r->r.error);
+    delete r;
+    return SB200_ERR_ASSERT;
+  }
+  *out = r;
+  return SB200_OK;
+}
+int sb200_circ_int_to_scalar(const uint8_t* magnitude_le, size_t len, uint8_t out32[32]) {
+  if ((!magnitude_le && len) || !out32) return SB200_ERR_ARG;
+  fl_to_bytes(circ_int_to_scalar(magnitude_le, len), out32);
+  return SB200_OK;
+}
 
 // ---- exchange for sharded proofs ------------------------------------------------------------
 int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out) {

@@ -4,12 +4,13 @@ All calls go through the C ABI (include/spartan_b200.h, spartan_b200_kernels.h).
 Bar: bit-exact (integer / byte work).
 """
 import ctypes as C
+import os
 import random
 
 import pytest
 
 import oracle_lib as O
-from common import ELL, LABEL, TAPE_SEED, canon, mont, rand_scalars
+from common import ELL, LABEL, TAPE_SEED, canon, mont, ragged_r1cs, rand_scalars
 
 pytestmark = pytest.mark.gpu
 
@@ -409,3 +410,43 @@ def test_large_round_trip_properties(sb):
     out = bytes(out)
     assert O.pt_add(out[:32], out[32:64]) == out[64:96]
     assert out[96:] == bytes(32)  # the all-zero row commits to the identity
+
+
+def test_pipelined_witness_upload(sb):
+    """A witness of >= 8 MiB coming from host memory is copied in pieces and committed piece by piece
+    (prover.inc): same bytes as the single-copy path and as the oracle, also when the padded tail of a
+    non-power-of-two witness cuts through the pieces."""
+    s = 18
+    n = 1 << s
+    # (a) synthetic 2^18, pieces 1 / default / maximum
+    oi, ov, oin = O.Instance.synthetic(n, n, 10, 11)
+    og = O.Gens(n, n, 10)
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, 10, 11)
+    pg = sb.NIZKGens.new(n, n, 10)
+    want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED, 8)
+    got = {}
+    try:
+        for pieces in ("1", None, "8", "3"):
+            if pieces is None:
+                os.environ.pop("SB200_H2D_PIECES", None)
+            else:
+                os.environ["SB200_H2D_PIECES"] = pieces
+            got[pieces] = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED).to_bytes()
+    finally:
+        os.environ.pop("SB200_H2D_PIECES", None)
+    for k, v in got.items():
+        assert v == want, "pieces=%s" % k
+    # (b) few constraints, 2^18 - 4133 variables: the zero padding starts inside the last piece
+    nc, nv, ni = 48, n - 4133, 3
+    A, B, Cm, vars_, inputs = ragged_r1cs(nc, nv, ni)
+    oi = O.Instance.new(nc, nv, ni, A, B, Cm)
+    pi = sb.Instance.new(nc, nv, ni, A, B, Cm)
+    vb, ib = canon(vars_), canon(inputs)
+    pv, pin = sb.VarsAssignment.new(vb), sb.InputsAssignment.new(ib)
+    assert pi.is_sat(pv, pin)
+    og = O.Gens(nc, nv, ni)
+    pg = sb.NIZKGens.new(nc, nv, ni)
+    want = O.nizk_prove(oi, vb, ib, og, LABEL, TAPE_SEED, 8)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == want
+    assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
