@@ -320,9 +320,18 @@ def main():
     # fmaheavy issues one IMAD.WIDE.U32 warp instruction per 4 cycles per SM sub-partition (measured:
     # profiles/r01_msm_fixed_2p20_v3.txt, 22.6 % inst rate at 80.8 % pipe-active) -> 8 lanes/clk/SMSP
     int_peak = 148 * 4 * 8 * sm_mhz * 1e6
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")) as f:
+            ent = json.load(f)["msm_fixed_kernel"].get(str(s))
+        if ent:
+            traffic, traffic_src = ent["bytes"], ent["source"]
+    except Exception:
+        pass
     roofline = {
         "kernel": "msm_fixed_kernel (commitment rows, %d x %d, %d-bit windows)" % (Ls, Rs, c), "bound": "hbm", "achieved": achieved,
-        "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": which,
+        "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read + write)",
+        "traffic_source": traffic_src, "algorithmic_bytes": alg_bytes, "peak_source": which,
         "kernel_ms": 1e3 * k_s, "share_of_step": k_s / (res_ms * 1e-3 / args.steps),
         "int_pipe": {"achieved_gimad_per_s": imad / k_s / 1e9 if k_s > 0 else 0.0, "peak_gimad_per_s": int_peak / 1e9,
                      "frac": (imad / k_s) / int_peak if k_s > 0 else 0.0,
