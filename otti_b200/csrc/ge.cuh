@@ -44,13 +44,25 @@ SB_HD ge_t ge_add_t(const ge_t& p, const ge_t& q) {
 template <class F>
 SB_HD ge_t ge_madd_t(const ge_t& p, const niels_t& q, bool neg) {
   fp_t ypx = fp_add(p.Y, p.X), ymx = fp_sub(p.Y, p.X);
-  fp_t A = F::mul(ymx, neg ? q.yplusx : q.yminusx);
-  fp_t B = F::mul(ypx, neg ? q.yminusx : q.yplusx);
+  // -Q = (y-x, y+x, -2dxy): limb-wise selects (a select between the two structs would go through local memory)
+  fp_t qa, qb;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    qa.v[i] = neg ? q.yplusx.v[i] : q.yminusx.v[i];
+    qb.v[i] = neg ? q.yminusx.v[i] : q.yplusx.v[i];
+  }
+  fp_t A = F::mul(ymx, qa);
+  fp_t B = F::mul(ypx, qb);
   fp_t C = F::mul(p.T, q.xy2d);
   fp_t D = fp_add(p.Z, p.Z);
   fp_t E = fp_sub(B, A), H = fp_add(B, A);
-  fp_t Fv = neg ? fp_add(D, C) : fp_sub(D, C);
-  fp_t G = neg ? fp_sub(D, C) : fp_add(D, C);
+  const fp_t dmc = fp_sub(D, C), dpc = fp_add(D, C);
+  fp_t Fv, G;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    Fv.v[i] = neg ? dpc.v[i] : dmc.v[i];
+    G.v[i] = neg ? dmc.v[i] : dpc.v[i];
+  }
   ge_t r;
   r.X = F::mul(E, Fv); r.Y = F::mul(G, H); r.Z = F::mul(Fv, G); r.T = F::mul(E, H);
   return r;

@@ -844,19 +844,21 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
     }
     if ((kw[0] | kw[1] | kw[2] | kw[3] | kw[4] | kw[5] | kw[6] | kw[7]) == 0) continue;
     const niels_t* tb = tbl + (size_t)j * epb;
+    // The entry of window w+1 is requested while window w is added.  Nothing may touch the loaded words before
+    // their window comes up (a sign fix-up at load time made every request wait for its own data: 14 % of the
+    // kernel's stall samples in profiles/r01_ncu_full_2p22_v5), so the sign of the digit travels to ge_madd.
     uint32_t carry = 0;
     int32_t d_next = msm_digit(kw, 0, c, carry);
     niels_t e_next;
-    if (d_next != 0) e_next = ldg_niels_signed(tb + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1), d_next < 0);
+    if (d_next != 0) e_next = ldg_niels(tb + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1));
     for (uint32_t w = 0; w < windows; w++) {
       const int32_t d = d_next;
       const niels_t e = e_next;
       if (w + 1 < windows) {
         d_next = msm_digit(kw, w + 1, c, carry);
-        if (d_next != 0)
-          e_next = ldg_niels_signed(tb + ((size_t)(w + 1) << (c - 1)) + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1), d_next < 0);
+        if (d_next != 0) e_next = ldg_niels(tb + ((size_t)(w + 1) << (c - 1)) + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1));
       }
-      if (d != 0) acc = ge_madd(acc, e, false);
+      if (d != 0) acc = ge_madd(acc, e, d < 0);
     }
   }
   if (extra_h != nullptr && split == 0 && wid == 0 && lane < windows) {

@@ -428,10 +428,17 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
   }
   // Window width of the device tables: every extra bit removes madds from the commitment kernel
   // (floor(252/c)+1 per term) and doubles the table.  Largest c whose table fits SB200_TABLE_MB
-  // (default 64 GiB of the 180 GB HBM: c = 16/16/15/14 at 2^16/2^20/2^22/2^24); SB200_MSM_WINDOW forces a value.
+  // (default: 112 GiB of the 180 GB HBM, less if the device has not got 24 GiB more than that free for the
+  // instance and the workspace: c = 16/16/16/15 at 2^16/2^20/2^22/2^24); SB200_MSM_WINDOW forces a value.
   uint32_t c = 8;
   {
-    size_t budget = (size_t)65536 << 20;
+    size_t budget = (size_t)114688 << 20;
+    {
+      size_t free_b = 0, total_b = 0;
+      const size_t reserve = (size_t)24 << 30;
+      if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
+        budget = std::min(budget, free_b > reserve + ((size_t)1 << 30) ? free_b - reserve : (size_t)1 << 30);
+    }
     if (const char* env = getenv("SB200_TABLE_MB")) {
       long v = atol(env);
       if (v > 0) budget = (size_t)v << 20;
