@@ -10,6 +10,9 @@
 #pragma once
 #include "fl.cuh"
 #include "mp.cuh"
+#ifdef SB_FP_KARATSUBA
+#include "../../tools/microbench/mp_karatsuba.cuh"
+#endif
 
 namespace sb {
 
@@ -188,7 +191,11 @@ __device__ __forceinline__ fp_t fp_reduce16_dev(const uint32_t* t) {
 }
 __device__ __forceinline__ fp_t fp_mul(const fp_t& a, const fp_t& b) {
   uint32_t t[16];
+#ifdef SB_FP_KARATSUBA  // tools/microbench only: measured slower, see tools/microbench/mp_karatsuba.cuh
+  mp_mul8_kara(t, a.v, b.v);
+#else
   mp_mul8(t, a.v, b.v);
+#endif
   return fp_reduce16_dev(t);
 }
 __device__ __forceinline__ fp_t fp_sqr(const fp_t& a) { return fp_mul(a, a); }

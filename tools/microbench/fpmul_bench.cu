@@ -93,17 +93,25 @@ int main() {
   for (int mode = 0; mode < 3; mode++)
     for (int blocks_per_sm = 0; blocks_per_sm <= 4; blocks_per_sm++) {
       int grid = blocks_per_sm == 0 ? 1 : 148 * blocks_per_sm, block = blocks_per_sm == 0 ? 32 : 128;
+      cudaEvent_t ev0, ev1;
+      cudaEventCreate(&ev0); cudaEventCreate(&ev1);
       for (int rep = 0; rep < 2; rep++) {
+        if (rep == 1) cudaEventRecord(ev0);
         if (mode == 0) bench<0><<<grid, block>>>(d, o, c, iters);
         else if (mode == 1) bench<1><<<grid, block>>>(d, o, c, iters);
         else bench<2><<<grid, block>>>(d, o, c, iters);
+        if (rep == 1) cudaEventRecord(ev1);
       }
       cudaError_t e = cudaDeviceSynchronize();
+      float kms = 0; cudaEventElapsedTime(&kms, ev0, ev1);
+      // whole-kernel figure: the clock64 figure below is block 0 alone, which overstates throughput when not every block is resident
+      if (blocks_per_sm > 0) printf("  kernel %.3f ms -> %.0f ns per warp-op per SMSP\n", kms, kms * 1e6 / ((double)iters * blocks_per_sm));
       long long cyc; cudaMemcpy(&cyc, c, 8, cudaMemcpyDeviceToHost);
       if (blocks_per_sm == 0 && mode < 2) cudaMemcpy(&ref[mode], o, sizeof(ge_t), cudaMemcpyDeviceToHost);
       printf("mode %d (%s) warps/SMSP %s: %.1f cycles per op  [%s]\n", mode, mode == 0 ? "ge_madd" : mode == 1 ? "ge_madd interleaved" : "fp_mul chain",
              blocks_per_sm == 0 ? "1 warp alone" : (blocks_per_sm == 1 ? "1" : blocks_per_sm == 2 ? "2" : blocks_per_sm == 3 ? "3" : "4"), (double)cyc / iters, cudaGetErrorString(e));
     }
   printf("results equal: %d\n", memcmp(&ref[0], &ref[1], sizeof(ge_t)) == 0);
+  { unsigned long long h = 1469598103934665603ull; const unsigned char* q = (const unsigned char*)&ref[0]; for (size_t i = 0; i < sizeof(ge_t); i++) h = (h ^ q[i]) * 1099511628211ull; printf("checksum %016llx\n", h); }
   return 0;
 }
