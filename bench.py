@@ -286,7 +286,13 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
 
     t = torch.tensor([res_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    per_rank = None
     if dist is not None:
+        mine = torch.tensor([res_ms / args.steps, e2e_ms / args.steps, float(sb.lib().sb200_bound_cpus())], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step": [round(float(x[0]), 4) for x in allr], "e2e_ms_per_step": [round(float(x[1]), 4) for x in allr],
+                    "host_cpus_bound": [int(x[2]) for x in allr]}
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     res_ms, e2e_ms = float(t[0]), float(t[1])
 
@@ -382,6 +388,8 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
     }
+    if per_rank is not None:
+        line["per_rank"] = per_rank
     if sharded is not None:
         line["sharded"] = sharded
     print(json.dumps(line), flush=True)

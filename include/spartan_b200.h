@@ -114,8 +114,13 @@ int sb200_comm_selftest(const sb200_comm_vt* comm, int rounds, uint8_t digest32_
 int sb200_comm_selftest_expected(int world, int rounds, uint8_t digest32_out[32]);
 
 /* Selects the CUDA device for the calling process (one process per GPU).
- * Fails with SB200_ERR_NO_DEVICE if it is not compute capability 10.x. */
+ * Fails with SB200_ERR_NO_DEVICE if it is not compute capability 10.x.
+ * With LOCAL_WORLD_SIZE > 1 (one rank per GPU under torchrun) the calling thread -- and the host worker threads the
+ * library creates from it later -- are bound to a slice of the cores next to the GPU (its PCI local_cpulist, split
+ * among the ranks that share it); SB200_BIND=0 turns that off, SB200_BIND=1 forces it for a single process.
+ * sb200_bound_cpus() = how many CPUs the last sb200_init bound the caller to (0 = affinity left alone). */
 int sb200_init(int device);
+int sb200_bound_cpus(void);
 
 /* Assignment::new(&[[u8;32]]) -> Result<Assignment, R1CSError>            lib.rs:65-89
  * SB200_ERR_INVALID_SCALAR if any of the n values is not a canonical scalar. */

@@ -88,7 +88,7 @@ class HostPool {
         int ranks = atoi(lw);
         if (ranks > 1) hw /= ranks;
       }
-      int n = hw > 2 ? hw - 2 : (hw == 2 ? 1 : 0);  // with two cores: this thread + the tape drawer
+      int n = hw > 1 ? hw - 1 : 0;  // this thread + n workers = one thread per core (the last worker draws the tape first)
       if (n > 10) n = 10;
       if (const char* e = getenv("SB200_HOST_THREADS")) n = atoi(e);
       if (n < 0) n = 0;

@@ -730,8 +730,6 @@ __device__ __forceinline__ int32_t msm_digit_at(const uint32_t* kp, uint32_t w, 
   for (uint32_t i = 0; i <= w; i++) d = msm_digit(kp, i, c, carry);
   return d;
 }
-// Sum over the lanes of a warp / over nw <= 32 values held by the first lanes, by shuffles (out-of-line
-// point addition: one copy per kernel).
 __device__ __forceinline__ ge_t shfl_down_ge(const ge_t& x, int o) {
   ge_t y;
 #pragma unroll
@@ -742,11 +740,6 @@ __device__ __forceinline__ ge_t shfl_down_ge(const ge_t& x, int o) {
     y.T.v[i] = __shfl_down_sync(0xffffffffu, x.T.v[i], o);
   }
   return y;
-}
-__device__ __forceinline__ ge_t warp_sum_ge_from(ge_t x, int first_offset) {
-#pragma unroll 1
-  for (int o = first_offset; o > 0; o >>= 1) x = ge_add_call(x, shfl_down_ge(x, o));
-  return x;
 }
 // ---- point sums with four lanes per addition
 // A tree level of a point sum leaves most lanes idle, and a lone warp pays the full latency of the nine dependent
@@ -809,16 +802,6 @@ __device__ __forceinline__ ge_t warp_sum_ge_n(const ge_t& x, uint32_t count) {
     if ((uint32_t)(o >> 2) < q) y = ge_add_quad(y, shfl_down_ge(y, o));
   return y;
 }
-__device__ __forceinline__ niels_t ldg_niels_signed(const niels_t* p, bool neg) {  // -P = (y-x, y+x, -2dxy)
-  niels_t e = ldg_niels(p);
-  if (neg) {
-    fp_t t = e.yplusx;
-    e.yplusx = e.yminusx;
-    e.yminusx = t;
-    e.xy2d = fp_neg(e.xy2d);
-  }
-  return e;
-}
 // Commitment rows: block (split, row) sums terms [split*B*tpt, (split+1)*B*tpt) of its row.  A thread
 // walks the windows of one term at a time, fetching the table entry of window w+1 while it adds the
 // entry of window w; partial sums are combined by warp shuffles, then across the (<= 8) warps.  The
@@ -869,7 +852,7 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
     for (uint32_t w = lane; w < windows; w += 32) {
       int32_t d = msm_digit_at(kw, w, c);
       if (d != 0)
-        acc = ge_madd(acc, ldg_niels_signed(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(d < 0 ? -d : d) - 1), d < 0), false);
+        acc = ge_madd(acc, ldg_niels(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(d < 0 ? -d : d) - 1)), d < 0);
     }
   }
   acc = warp_sum_ge_n(acc, 32);
@@ -999,21 +982,6 @@ cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const
 // last-block-done tree.  The result is left in EXTENDED coordinates (optionally in mapped host
 // memory, followed by a flag): one point compression is ~280 dependent field multiplications,
 // which a host core does in ~4 us and a lone GPU thread in ~40 us.
-__device__ __forceinline__ ge_t warp_sum_ge(ge_t x) {
-#pragma unroll 1
-  for (int o = 16; o > 0; o >>= 1) {
-    ge_t y;
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-      y.X.v[i] = __shfl_down_sync(0xffffffffu, x.X.v[i], o);
-      y.Y.v[i] = __shfl_down_sync(0xffffffffu, x.Y.v[i], o);
-      y.Z.v[i] = __shfl_down_sync(0xffffffffu, x.Z.v[i], o);
-      y.T.v[i] = __shfl_down_sync(0xffffffffu, x.T.v[i], o);
-    }
-    x = ge_add_call(x, y);
-  }
-  return x;
-}
 // valid in thread 0; smem: ge_t[blockDim.x / 32].  The second level only runs the shuffle steps that can
 // still carry data (log2 of the number of warps): every skipped step is a full point addition of latency.
 __device__ __forceinline__ ge_t block_sum_ge(ge_t x, ge_t* smem) {

@@ -18,6 +18,7 @@
 #include "../../include/spartan_b200_kernels.h"
 #include "host/objects.hpp"
 #include "host/proof.hpp"
+#include "host/affinity.hpp"
 
 namespace sbh {
 
@@ -28,6 +29,7 @@ static thread_local double g_profile[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 
 static std::atomic<uint64_t> g_h2d_bytes{0}, g_d2h_bytes{0};  // one proof at a time per process (prove_mu); counted from two threads
 
 static bool g_device_ok = false;
+static int g_bound_cpus = 0;
 static int ensure_device() {
   if (g_device_ok) return SB200_OK;
   int n = 0;
@@ -165,8 +167,11 @@ int sb200_init(int device) {
   }
   SB_CUDA(cudaSetDevice(device));
   g_device_ok = false;
+  g_bound_cpus = sbh::bind_near_device(device, n);  // one process per GPU: host threads next to the GPU (host/affinity.hpp)
   return ensure_device();
 }
+// CPUs the calling thread was bound to by the last sb200_init (0 = affinity left alone)
+int sb200_bound_cpus(void) { return g_bound_cpus; }
 
 int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, const uint64_t* const rows[3],
                                const uint64_t* const cols[3], const uint8_t* const vals32[3], const uint64_t nnz[3],

@@ -450,3 +450,46 @@ def test_pipelined_witness_upload(sb):
     proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
     assert proof.to_bytes() == want
     assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+
+
+@pytest.mark.parametrize("s", [20, 22])
+def test_full_size_properties(sb, s):
+    """BASELINE.json's full sizes (2^20 of the README comparison, 2^22 of configs[4]), where the oracle is too slow
+    to be the checker: size-independent properties.  Proof length = closed form (App. A.4); prove -> verify round trip
+    on the device; determinism (same tape seed -> same bytes, resident witness == witness from host memory, i.e. the
+    pipelined upload); a different tape seed gives a different proof that also verifies; a flipped proof byte, a wrong
+    input and an unsatisfying witness are rejected."""
+    n = 1 << s
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, 10, 0x51 + s)
+    pg = sb.NIZKGens.new(n, n, 10)
+    assert pi.is_sat(pv, pin)
+    proof = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED)
+    b = proof.to_bytes()
+    lL = s // 2
+    dpp = lambda k: 32 + 32 + 8 + 32 * k + 32 + 32
+    sc = lambda rounds, k: (8 + 32 * rounds) * 2 + 8 + rounds * dpp(k)
+    want_len = (8 + 32 * (1 << lL)) + sc(s, 4) + 128 + 352 + 64 + sc(s + 1, 3) + 32 + (2 * (8 + 32 * (s - lL)) + 128) + 64
+    assert proof.r1cs_sat_proof_len == want_len
+    if s == 20:
+        assert want_len == 47024  # Spartan/README.md:376, the only byte-level figure the reference publishes
+    assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    os.environ["SB200_H2D_PIECES"] = "1"
+    try:
+        assert sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED).to_bytes() == b
+    finally:
+        os.environ.pop("SB200_H2D_PIECES", None)
+    other = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), bytes(64))
+    assert other.to_bytes() != b and len(other.to_bytes()) == len(b)
+    assert other.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    rng = random.Random(s)
+    for off in (40, len(b) // 3, len(b) - 5):
+        bad = bytearray(b)
+        bad[off] ^= 1 << rng.randrange(8)
+        with pytest.raises(sb.ProofVerifyError):
+            sb.NIZK(bytes(bad)).verify(pi, pin, sb.Transcript.new(LABEL), pg)
+    wrong = canon([(int.from_bytes(bytes(pin.data[:32]), "little") + 1) % ELL]) + bytes(pin.data[32:])
+    with pytest.raises(sb.ProofVerifyError):
+        proof.verify(pi, sb.InputsAssignment.new(wrong), sb.Transcript.new(LABEL), pg)
+    vb = bytearray(bytes(pv.data))
+    vb[0] ^= 1
+    assert not pi.is_sat(sb.VarsAssignment.new(bytes(vb)), pin)
