@@ -303,9 +303,24 @@ static inline void ge_batch_to_niels(const Ge* pts, size_t n, GeNiels* out) {
 }
 
 // Fixed-base table: 32 windows of 8 bits, entries d*256^w*P for d = 1..255.
+// device fp_t (8 LE words, any representative < 2^256) -> host field element
+static inline Fe fe_from_loose(const uint8_t* p) {
+  Fe r = fe_frombytes(p);  // ignores bit 255
+  if (p[31] & 0x80) r.v[0] += 19;  // 2^255 = 19 (mod p); limbs have 13 bits of headroom
+  return r;
+}
+
+// k * P for one of the seven generators of the Fiat-Shamir tail.  Two tables:
+//   narrow  32 windows x 255 multiples (unsigned 8-bit digits), built on the host, ~1 MB, cache resident;
+//   wide    a host copy of this base's slice of the commitment kernel's window table (device format: ww windows x
+//           2^(wc-1) entries of 96 bytes = (y+x, y-x, 2dxy) as 8 LE words each, signed radix-2^wc digits).  Half as
+//           many additions per multiplication at wc = 16; the entries are prefetched before the additions start, so
+//           the table need not fit any cache.
 struct FixedBase {
   std::vector<GeNiels> tbl;  // [32][255]
   Ge point;
+  const uint8_t* wide = nullptr;
+  uint32_t wc = 0, ww = 0;
   void build(const Ge& p) {
     point = p;
     std::vector<Ge> ext(32 * 255);
@@ -321,15 +336,52 @@ struct FixedBase {
     tbl.resize(32 * 255);
     ge_batch_to_niels(ext.data(), ext.size(), tbl.data());
   }
-  // acc += k * P, k canonical 32 bytes
-  void mul_acc(Ge& acc, const uint8_t k[32]) const {
-    for (int w = 0; w < 32; w++)
-      if (k[w]) acc = ge_madd(acc, tbl[w * 255 + k[w] - 1]);
+  void set_wide(const uint8_t* entries, uint32_t c, uint32_t windows) {
+    wide = entries;
+    wc = c;
+    ww = windows;
   }
-  // windows [w0, w1) only: k*P is a sum over windows, so one multiplication can be split over threads
-  void mul_acc_range(Ge& acc, const uint8_t k[32], int w0, int w1) const {
-    for (int w = w0; w < w1; w++)
-      if (k[w]) acc = ge_madd(acc, tbl[w * 255 + k[w] - 1]);
+  // acc += k * P, k canonical 32 bytes
+  void mul_acc(Ge& acc, const uint8_t k[32]) const { mul_acc_range(acc, k, 0, 32); }
+  // the part [lo, hi) / 32 of the windows only: k*P is a sum over windows, so one multiplication can be split over threads
+  void mul_acc_range(Ge& acc, const uint8_t k[32], int lo, int hi) const {
+    if (wide == nullptr) {
+      for (int w = lo; w < hi; w++)
+        if (k[w]) acc = ge_madd(acc, tbl[w * 255 + k[w] - 1]);
+      return;
+    }
+    const uint32_t w0 = ww * (uint32_t)lo / 32, w1 = ww * (uint32_t)hi / 32;
+    uint32_t kw[8];
+    memcpy(kw, k, 32);
+    // signed digits in (-2^(c-1), 2^(c-1)] with the running carry: the recoding of sb::msm_digit (ge.cuh)
+    const uint32_t half = 1u << (wc - 1), mask = (1u << wc) - 1;
+    const uint8_t* e[64];
+    bool neg[64];
+    uint32_t carry = 0;
+    for (uint32_t w = 0; w < w1 && w < 64; w++) {
+      const uint32_t bit = w * wc, limb = bit >> 5, sh = bit & 31;
+      const uint64_t two = ((uint64_t)(limb < 7 ? kw[limb + 1] : 0u) << 32) | kw[limb];
+      uint32_t d = ((uint32_t)(two >> sh) & mask) + carry;
+      const bool n = d > half;
+      carry = n ? 1u : 0u;
+      if (n) d = (1u << wc) - d;
+      e[w] = nullptr;
+      if (w >= w0 && d != 0) {
+        e[w] = wide + (((size_t)w << (wc - 1)) + (d - 1)) * 96;
+        neg[w] = n;
+        __builtin_prefetch(e[w]);
+        __builtin_prefetch(e[w] + 64);
+      }
+    }
+    for (uint32_t w = w0; w < w1 && w < 64; w++) {
+      if (e[w] == nullptr) continue;
+      GeNiels q{fe_from_loose(e[w]), fe_from_loose(e[w] + 32), fe_from_loose(e[w] + 64)};
+      if (neg[w]) {  // -P = (y-x, y+x, -2dxy)
+        std::swap(q.ypx, q.ymx);
+        q.t2d = fe_neg(q.t2d);
+      }
+      acc = ge_madd(acc, q);
+    }
   }
 };
 

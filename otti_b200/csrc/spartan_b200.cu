@@ -463,6 +463,32 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
     delete g;
     return SB200_ERR_CUDA;
   }
+  // Host copies of the table slices of the seven generators of the Fiat-Shamir tail (FixedBase::wide, hge.hpp): the
+  // stream points 0..4 (gens_3 / gens_4), Q = point R and h = point R+1, wherever they are among the device bases
+  // [G_0..G_{R-1}, h, Q].  SB200_HOST_WIDE=0 keeps the narrow host tables.
+  {
+    const char* hw = getenv("SB200_HOST_WIDE");
+    if (c >= 10 && !(hw && atoi(hw) == 0)) {
+      const size_t bytes = g->table.entries_per_base() * (size_t)96;  // sizeof(niels_t)
+      FixedBase* fbs[7] = {&g->fb_G4[0], &g->fb_G4[1], &g->fb_G4[2], &g->fb_G4[3], &g->fb_h4, &g->fb_Q, &g->fb_h};
+      const size_t point_of[7] = {0, 1, 2, 3, 4, (size_t)R, (size_t)R + 1};
+      SB_CUDA(cudaDeviceSynchronize());
+      for (int k = 0; k < 7; k++) {
+        const size_t pi = point_of[k];
+        long di = pi < R ? (long)pi : (pi == R ? (long)R + 1 : (pi == (size_t)R + 1 ? (long)R : -1));
+        if (di < 0) continue;
+        g->wide_store[k].resize(bytes);
+        cudaError_t e2 = cudaMemcpy(g->wide_store[k].data(), reinterpret_cast<const uint8_t*>(g->table.tbl) + (size_t)di * bytes, bytes,
+                                    cudaMemcpyDeviceToHost);
+        if (e2 != cudaSuccess) {
+          set_error(std::string("copying a table slice to the host: ") + cudaGetErrorString(e2));
+          delete g;
+          return SB200_ERR_CUDA;
+        }
+        fbs[k]->set_wide(g->wide_store[k].data(), g->table.c, g->table.windows);
+      }
+    }
+  }
   *out = reinterpret_cast<sb200_gens*>(g);
   return SB200_OK;
 }
