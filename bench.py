@@ -64,8 +64,13 @@ class ClockSampler:
 
     def start(self):
         try:
+            def unbind():  # sb200_init bound this rank to its slice of the host cores: the sampler must not steal them
+                try:
+                    os.sched_setaffinity(0, range(os.cpu_count() or 1))
+                except Exception:
+                    pass
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, preexec_fn=unbind)
         except Exception:
             self.p = None
 
