@@ -328,8 +328,8 @@ def main():
     achieved = alg_bytes / k_s / 1e9 if k_s > 0 else 0.0
     imad = madds * 7 * 75  # IMAD.WIDE.U32 per F_p product: 64 partial products + 8 (x38 fold) + 3 (cuobjdump, fp.cuh)
     sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
-    # fmaheavy issues one IMAD.WIDE.U32 warp instruction per 4 cycles per SM sub-partition (measured:
-    # profiles/r01_msm_fixed_2p20_v3.txt, 22.6 % inst rate at 80.8 % pipe-active) -> 8 lanes/clk/SMSP
+    # fmaheavy issues one IMAD.WIDE.U32 warp instruction per 4 cycles per SM sub-partition (measured with
+    # tools/microbench/fpmul_bench under ncu: 523 IMAD.WIDE per mixed addition, 2435 cycles at 85 % pipe-active) -> 8 lanes/clk/SMSP
     int_peak = 148 * 4 * 8 * sm_mhz * 1e6
     traffic, traffic_src = None, None
     try:
@@ -347,7 +347,7 @@ def main():
         "int_pipe": {"achieved_gimad_per_s": imad / k_s / 1e9 if k_s > 0 else 0.0, "peak_gimad_per_s": int_peak / 1e9,
                      "frac": (imad / k_s) / int_peak if k_s > 0 else 0.0,
                      "note": "the kernel's real limiter: 64-bit integer multiply-adds (IMAD.WIDE.U32) on the fmaheavy pipe; "
-                             "ncu sm__pipe_fmaheavy_cycles_active 80.8 % at 2^20 (profiles/)"},
+                             "ncu sm__pipe_fmaheavy_cycles_active 75.9 % at 2^22 (profiles/r01_ncu_full_2p22_v5.txt, r01_summary.md)"},
         "hbm_kernel_sample": {"kernel": "sc_cubic_kernel<false> (round 0: 4 tables x 32 B x 2^%d read)" % s,
                               "achieved": 4 * 32 * n / prof["sc_cubic_round0_kernel"] / 1e9 if prof["sc_cubic_round0_kernel"] > 0 else 0.0,
                               "unit": "GB/s", "kernel_ms": 1e3 * prof["sc_cubic_round0_kernel"]},
