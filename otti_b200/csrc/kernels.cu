@@ -455,30 +455,34 @@ __global__ void __launch_bounds__(256) sc_cubic_lat_kernel(fl_t* __restrict__ T,
   __shared__ fl_t sred[8][4];
   const size_t h = newlen >> 1;
   const uint32_t k = threadIdx.x & 3, pl = threadIdx.x >> 2;
-  const size_t pair = (size_t)blockIdx.x * 64 + pl;
   fl_t* X = k == 0 ? T : k == 1 ? A : k == 2 ? B : C;
-  fl_t lo = fl_zero(), hi = fl_zero();
-  if (pair < h) {
-    if (BIND) {
-      fl_t a0 = ld_fl(X + pair), a1 = ld_fl(X + pair + newlen), b0 = ld_fl(X + pair + h), b1 = ld_fl(X + pair + h + newlen);
-      lo = bind1<FlInl>(a0, a1, r);
-      hi = bind1<FlInl>(b0, b1, r);
-      st_fl(X + pair, lo);
-      st_fl(X + pair + h, hi);
-    } else {
-      lo = ld_fl(X + pair);
-      hi = ld_fl(X + pair + h);
-    }
-  }
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 4) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
-  const fl_t d = fl_sub(hi, lo), p2 = fl_add(hi, d), p3 = fl_add(p2, d);  // values at 0, 2, 3 of this table's line
-  sv[pl][0][k] = lo;
-  sv[pl][1][k] = p2;
-  sv[pl][2][k] = p3;
-  __syncthreads();
   fl_t e = fl_zero();
-  if (k < 3 && pair < h)  // comb(T,A,B,C) = T*(A*B - C) at point k (sumcheck.rs:622-650, r1csproof.rs:84-88)
-    e = fl_mul(sv[pl][k][0], fl_sub(fl_mul(sv[pl][k][1], sv[pl][k][2]), sv[pl][k][3]));
+  // 64 pairs per block and pass; the pass count is the same for every thread of a block (barriers inside)
+  for (size_t base = (size_t)blockIdx.x * 64; base < h; base += (size_t)gridDim.x * 64) {
+    const size_t pair = base + pl;
+    fl_t lo = fl_zero(), hi = fl_zero();
+    if (pair < h) {
+      if (BIND) {
+        fl_t a0 = ld_fl(X + pair), a1 = ld_fl(X + pair + newlen), b0 = ld_fl(X + pair + h), b1 = ld_fl(X + pair + h + newlen);
+        lo = bind1<FlInl>(a0, a1, r);
+        hi = bind1<FlInl>(b0, b1, r);
+        st_fl(X + pair, lo);
+        st_fl(X + pair + h, hi);
+      } else {
+        lo = ld_fl(X + pair);
+        hi = ld_fl(X + pair + h);
+      }
+    }
+    const fl_t d = fl_sub(hi, lo), p2 = fl_add(hi, d), p3 = fl_add(p2, d);  // values at 0, 2, 3 of this table's line
+    if (base != (size_t)blockIdx.x * 64) __syncthreads();  // the previous pass has read sv
+    sv[pl][0][k] = lo;
+    sv[pl][1][k] = p2;
+    sv[pl][2][k] = p3;
+    __syncthreads();
+    if (k < 3 && pair < h)  // comb(T,A,B,C) = T*(A*B - C) at point k (sumcheck.rs:622-650, r1csproof.rs:84-88)
+      e = fl_add(e, fl_mul(sv[pl][k][0], fl_sub(fl_mul(sv[pl][k][1], sv[pl][k][2]), sv[pl][k][3])));
+  }
   quad_grid_sum(e, sred, partials, counter, result, mb);
 }
 template <bool BIND>
@@ -488,29 +492,44 @@ __global__ void __launch_bounds__(256) sc_quad_lat_kernel(fl_t* __restrict__ Z, 
   __shared__ fl_t sred[8][4];
   const size_t h = newlen >> 1;
   const uint32_t k = threadIdx.x & 3, pl = threadIdx.x >> 2;
-  const size_t pair = (size_t)blockIdx.x * 64 + pl;
   fl_t* X = (k & 1) ? Q : Z;
-  const size_t at = pair + ((k & 2) ? h : 0);
-  fl_t v = fl_zero();
-  if (pair < h) {
-    if (BIND) {
-      v = bind1<FlInl>(ld_fl(X + at), ld_fl(X + at + newlen), r);
-      st_fl(X + at, v);
-    } else {
-      v = ld_fl(X + at);
-    }
-  }
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 2) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
-  sv[pl][k] = v;
-  __syncthreads();
   fl_t e = fl_zero();
-  if (pair < h) {  // sumcheck.rs:459-467
-    if (k == 0) e = fl_mul(sv[pl][0], sv[pl][1]);
-    else if (k == 1) e = fl_mul(fl_sub(fl_add(sv[pl][2], sv[pl][2]), sv[pl][0]), fl_sub(fl_add(sv[pl][3], sv[pl][3]), sv[pl][1]));
+  for (size_t base = (size_t)blockIdx.x * 64; base < h; base += (size_t)gridDim.x * 64) {
+    const size_t pair = base + pl;
+    const size_t at = pair + ((k & 2) ? h : 0);
+    fl_t v = fl_zero();
+    if (pair < h) {
+      if (BIND) {
+        v = bind1<FlInl>(ld_fl(X + at), ld_fl(X + at + newlen), r);
+        st_fl(X + at, v);
+      } else {
+        v = ld_fl(X + at);
+      }
+    }
+    if (base != (size_t)blockIdx.x * 64) __syncthreads();  // the previous pass has read sv
+    sv[pl][k] = v;
+    __syncthreads();
+    if (pair < h) {  // sumcheck.rs:459-467
+      if (k == 0) e = fl_add(e, fl_mul(sv[pl][0], sv[pl][1]));
+      else if (k == 1) e = fl_add(e, fl_mul(fl_sub(fl_add(sv[pl][2], sv[pl][2]), sv[pl][0]), fl_sub(fl_add(sv[pl][3], sv[pl][3]), sv[pl][1])));
+    }
   }
   quad_grid_sum(e, sred, partials, counter, result, mb);
 }
 static constexpr size_t kLatPairs = 8192;  // rounds with at most this many pairs run the latency variants
+static size_t lat_pairs_setting() {  // SB200_SC_LAT_PAIRS: experiment knob (the four-threads-per-pair kernels loop over 64-pair passes)
+  static const size_t v = [] {
+    const char* e = getenv("SB200_SC_LAT_PAIRS");
+    return e ? (size_t)strtoull(e, nullptr, 10) : kLatPairs;
+  }();
+  return v;
+}
+static inline unsigned lat_grid(size_t pairs, const ScWork& w) {
+  size_t g = (pairs + 63) / 64, cap = ((size_t)w.max_blocks * 3) / 4;  // the partials buffer holds max_blocks * 3 scalars, four per block here
+  if (const char* e = getenv("SB200_SC_LAT_BLOCKS")) cap = std::min<size_t>(cap, (size_t)atoi(e));
+  return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
+}
 static constexpr unsigned kCompactBlocks = 148;  // rounds with at most one block per SM run the compact kernels
 static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
   size_t g = (pairs + 255) / 256;
@@ -523,9 +542,8 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
-  if (newlen / 2 <= kLatPairs && w.max_blocks >= kLatPairs / 64) {
-    unsigned gl = (unsigned)((newlen / 2 + 63) / 64);
-    if (gl < 1) gl = 1;
+  if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
+    unsigned gl = lat_grid(newlen / 2, w);
     if (do_bind) sc_cubic_lat_kernel<true><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
     else sc_cubic_lat_kernel<false><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
     return SB_LAUNCHED();
@@ -541,9 +559,8 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
   size_t newlen = do_bind ? n_old / 2 : n_old;
   unsigned g = sc_grid(newlen / 2, w);
   Mailbox mb{w.host_result, w.host_flag, w.seq};
-  if (newlen / 2 <= kLatPairs && w.max_blocks >= kLatPairs / 64) {
-    unsigned gl = (unsigned)((newlen / 2 + 63) / 64);
-    if (gl < 1) gl = 1;
+  if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
+    unsigned gl = lat_grid(newlen / 2, w);
     if (do_bind) sc_quad_lat_kernel<true><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
     else sc_quad_lat_kernel<false><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
     return SB_LAUNCHED();
