@@ -81,7 +81,17 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   static constexpr int kMaxPieces = 8;
   cudaStream_t copy_stream = nullptr, msm_stream[2] = {nullptr, nullptr};
   cudaEvent_t ev_piece[kMaxPieces] = {}, ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+  // sharded proofs: the peers' vars_canon buffers mapped through CUDA IPC (prover.inc p2p_setup)
+  bool p2p_tried = false, p2p_ok = false;
+  std::vector<sb::fl_t*> peer_vars;
+  void close_peers() {
+    for (sb::fl_t*& p : peer_vars) {
+      if (p) cudaIpcCloseMemHandle(p);
+      p = nullptr;
+    }
+  }
   ~Workspace() {
+    close_peers();
     for (int i = 0; i < 4; i++) if (ev[i]) cudaEventDestroy(ev[i]);
     for (int i = 0; i < kMaxPieces; i++) if (ev_piece[i]) cudaEventDestroy(ev_piece[i]);
     if (ev_fork) cudaEventDestroy(ev_fork);

@@ -131,3 +131,25 @@ def test_host_tail_rounds_do_not_change_the_proof(world, tail, s, tmp_path):
     want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED)
     for r in _run_sharded(world, "syn:%d" % s, tmp_path, {"SB200_HOST_TAIL_LOG": str(tail)}):
         assert r[16:] == want
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,case", [(2, "syn:16"), (4, "syn:16"), (4, "rag:48,40000,3"), (8, "rag:48,33000,3")])
+def test_sharded_witness_exchange(world, case, tmp_path):
+    """Witnesses of >= 1 MiB: each rank uploads only its block of commitment rows and reads the other blocks from the
+    peers' HBM (CUDA IPC, prover.inc p2p_setup) -- also when the zero padding of a non-power-of-two witness leaves some
+    ranks a short or empty block.  Same bytes as the oracle, with and without the exchange."""
+    kind, arg = case.split(":")
+    if kind == "syn":
+        n = 1 << int(arg)
+        oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x0771)
+        og = O.Gens(n, n, 10)
+    else:
+        nc, nv, ni = (int(x) for x in arg.split(","))
+        A, B, Cm, v, i = ragged_r1cs(nc, nv, ni)
+        oi, ov, oin = O.Instance.new(nc, nv, ni, A, B, Cm), canon(v), canon(i)
+        og = O.Gens(nc, nv, ni)
+    want = O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED, 8)
+    for env in (None, {"SB200_P2P": "0"}):
+        for r in _run_sharded(world, case, tmp_path, env):
+            assert r[16:] == want
