@@ -118,9 +118,10 @@ cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cud
 cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC, size_t n, const ScWork& w, cudaStream_t s);
 
 // Bullet reduction scalar side (nizk/bullet.rs:71-118), see kernels.cu
-cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize,
-                          bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR,
-                          cudaStream_t s);
+// (a_in, b_in) are read only; with do_fold the folded vectors go to (a_out, b_out) -- a different pair of buffers
+cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t* b_out, const fl_t* coeff_in, fl_t* coeff_out,
+                          uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL,
+                          fl_t* sR, cudaStream_t s);
 // s[g] = from_mont(d * coeff[g]) for g < R                            (nizk/mod.rs:483-490)
 cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s);
 

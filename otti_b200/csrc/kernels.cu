@@ -667,18 +667,44 @@ __device__ __forceinline__ fl_t fl_from_mont_c(const fl_t& m) {
   one.v[0] = 1;
   return fl_mul_call(m, one);
 }
-__global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, const fl_t* coeff_in, fl_t* coeff_out,
-                                                           uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv,
-                                                           fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR) {
+// Grid: ceil(R / 512) "row" blocks + one "fold" block, so that a round costs five dependent multiplications instead
+// of one SM working through every loop.  A row block derives what it needs from the UNFOLDED vectors (the fold of one
+// entry of a and of one coefficient are three multiplications), the fold block writes the folded a, b, coeff for the
+// next round into the other buffer of a ping-pong pair -- the row blocks never read what it writes -- and adds the
+// two inner products and the blind rows.
+static constexpr int kBulletThreads = 512;
+__global__ void __launch_bounds__(kBulletThreads) bullet_step_kernel(const fl_t* __restrict__ a_in, const fl_t* __restrict__ b_in,
+                                                                     fl_t* __restrict__ a_out, fl_t* __restrict__ b_out,
+                                                                     const fl_t* __restrict__ coeff_in, fl_t* __restrict__ coeff_out,
+                                                                     uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv,
+                                                                     fl_t blind_L, fl_t blind_R, fl_t* __restrict__ sL, fl_t* __restrict__ sR) {
   __shared__ fl_t smem[2 * 32];
-  uint32_t n = n_cur;
-  const uint32_t nco_in = Rsize / n_cur;
+  const uint32_t n = do_fold ? n_cur / 2 : n_cur, half = n / 2;
+  if (blockIdx.x + 1 < gridDim.x) {  // row block: the two MSM scalar rows over the ORIGINAL bases
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n <= 1 || g >= Rsize) return;
+    const uint32_t t = g / n, pos = g % n, j = pos >= half ? pos - half : half + pos;
+    fl_t co, aj;
+    if (do_fold) {
+      co = FlCall::mul(ld_fl(coeff_in + (t >> 1)), (t & 1) ? u : u_inv);
+      aj = fl_add(FlCall::mul(ld_fl(a_in + j), u), FlCall::mul(u_inv, ld_fl(a_in + n + j)));
+    } else {
+      co = ld_fl(coeff_in + t);
+      aj = ld_fl(a_in + j);
+    }
+    const fl_t sc = fl_from_mont_c(FlCall::mul(aj, co));
+    st_fl(sL + g, pos >= half ? sc : fl_zero());
+    st_fl(sR + g, pos >= half ? fl_zero() : sc);
+    return;
+  }
+  // fold block
+  const fl_t *a = a_in, *b = b_in;
   if (do_fold) {
-    n = n_cur / 2;
+    const uint32_t nco_in = Rsize / n_cur;
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
-      fl_t al = ld_fl(a + i), ar = ld_fl(a + n + i), bl = ld_fl(b + i), br = ld_fl(b + n + i);
-      st_fl(a + i, fl_add(FlCall::mul(al, u), FlCall::mul(u_inv, ar)));
-      st_fl(b + i, fl_add(FlCall::mul(bl, u_inv), FlCall::mul(u, br)));
+      fl_t al = ld_fl(a_in + i), ar = ld_fl(a_in + n + i), bl = ld_fl(b_in + i), br = ld_fl(b_in + n + i);
+      st_fl(a_out + i, fl_add(FlCall::mul(al, u), FlCall::mul(u_inv, ar)));
+      st_fl(b_out + i, fl_add(FlCall::mul(bl, u_inv), FlCall::mul(u, br)));
     }
     for (uint32_t t = threadIdx.x; t < nco_in; t += blockDim.x) {
       fl_t c = ld_fl(coeff_in + t);
@@ -686,10 +712,10 @@ __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, con
       st_fl(coeff_out + 2 * t + 1, FlCall::mul(c, u));
     }
     __syncthreads();
+    a = a_out;
+    b = b_out;
   }
   if (n <= 1) return;
-  const fl_t* coeff = do_fold ? coeff_out : coeff_in;
-  const uint32_t half = n / 2;
   fl_t c[2];
   c[0] = c[1] = fl_zero();
   for (uint32_t i = threadIdx.x; i < half; i += blockDim.x) {
@@ -698,29 +724,21 @@ __global__ void __launch_bounds__(1024) bullet_step_kernel(fl_t* a, fl_t* b, con
     c[1] = fl_add(c[1], FlCall::mul(ar, bl));
   }
   block_sum_fl<2>(c, smem);
-  const size_t stride = (size_t)Rsize + 2;
-  (void)stride;
-  for (uint32_t g = threadIdx.x; g < Rsize; g += blockDim.x) {
-    uint32_t t = g / n, pos = g % n;
-    fl_t co = ld_fl(coeff + t);
-    if (pos >= half) {
-      st_fl(sL + g, fl_from_mont_c(FlCall::mul(ld_fl(a + (pos - half)), co)));
-      st_fl(sR + g, fl_zero());
-    } else {
-      st_fl(sR + g, fl_from_mont_c(FlCall::mul(ld_fl(a + half + pos), co)));
-      st_fl(sL + g, fl_zero());
+  if (threadIdx.x < 4) {  // rows have stride R + 2: [R] = H (blind), [R + 1] = Q (inner product); canonical form
+    const fl_t v = threadIdx.x == 0 ? blind_L : threadIdx.x == 1 ? blind_R : fl_zero();
+    if (threadIdx.x < 2) st_fl((threadIdx.x == 0 ? sL : sR) + Rsize, fl_from_mont_c(v));
+    if (threadIdx.x == 0) {
+      st_fl(sL + Rsize + 1, fl_from_mont_c(c[0]));
+      st_fl(sR + Rsize + 1, fl_from_mont_c(c[1]));
     }
   }
-  if (threadIdx.x == 0) {
-    st_fl(sL + Rsize, fl_from_mont_c(blind_L));
-    st_fl(sL + Rsize + 1, fl_from_mont_c(c[0]));
-    st_fl(sR + Rsize, fl_from_mont_c(blind_R));
-    st_fl(sR + Rsize + 1, fl_from_mont_c(c[1]));
-  }
 }
-cudaError_t k_bullet_step(fl_t* a, fl_t* b, fl_t* coeff_in, fl_t* coeff_out, uint32_t n_cur, uint32_t Rsize, bool do_fold,
-                          fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL, fl_t* sR, cudaStream_t s) {
-  bullet_step_kernel<<<1, 1024, 0, s>>>(a, b, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv, blind_L, blind_R, sL, sR);
+cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t* b_out, const fl_t* coeff_in, fl_t* coeff_out,
+                          uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL,
+                          fl_t* sR, cudaStream_t s) {
+  const unsigned row_blocks = (Rsize + kBulletThreads - 1) / kBulletThreads;
+  bullet_step_kernel<<<row_blocks + 1, kBulletThreads, 0, s>>>(a_in, b_in, a_out, b_out, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv,
+                                                              blind_L, blind_R, sL, sR);
   return SB_LAUNCHED();
 }
 __global__ void scale_from_mont_kernel(const fl_t* __restrict__ coeff, fl_t d, uint32_t n, fl_t* __restrict__ out) {
