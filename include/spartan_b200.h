@@ -249,6 +249,30 @@ int sb200_nizk_verify(const sb200_instance* inst, const uint8_t* inputs32, uint6
  *             [12] seconds inside the exchange hook, [13] exchange calls, [14] world, [15] reserved */
 int sb200_last_prove_profile(double out[16]);
 
+/* ---- SNARK mode, first half: the computation commitment (SNARK::prove is not built).
+ * SNARKGens::new(num_cons, num_vars, num_inputs, num_nz_entries)          lib.rs:279-303
+ *   only the part SNARK::encode reads: gens_r1cs_eval = R1CSCommitmentGens::new(b"gens_r1cs_eval", ...)
+ *   (r1csinstance.rs:29-43, sparse_mlpoly.rs:301-327) and its window tables in HBM.  Arguments as in the reference
+ *   (unpadded; num_nz_entries = the maximum number of non-zero entries of A, B, C).
+ *   SB200_ERR_ASSERT where the reference asserts (num_inputs < num_vars, r1csinstance.rs:36). */
+typedef struct sb200_snark_gens sb200_snark_gens; /* libspartan::SNARKGens (lib.rs:273-277) */
+int sb200_snark_gens_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t num_nz_entries,
+                         sb200_snark_gens** out);
+void sb200_snark_gens_free(sb200_snark_gens* gens);
+/* SNARK::encode(&inst, &gens) -> (ComputationCommitment, ComputationDecommitment)    lib.rs:321-333
+ *   -> R1CSInstance::commit r1csinstance.rs:285-297 -> SparseMatPolynomial::multi_commit sparse_mlpoly.rs:485-506.
+ * Public and deterministic (no transcript, no randomness).  comm_out (release with sb200_free): the fields of
+ * R1CSCommitment (r1csinstance.rs:46-51; not Serialize in the reference) as three little-endian u64 -- num_cons,
+ * num_vars, num_inputs, padded -- followed by the bincode 1.3 serialisation of SparseMatPolyCommitment
+ * { batch_size, num_ops, num_mem_cells, comm_comb_ops, comm_comb_mem } (sparse_mlpoly.rs:329-337).
+ * The decommitment (the dense representation) is rebuilt from the instance when needed and is not returned.
+ * SB200_ERR_ASSERT where the reference asserts (generators made for other sizes, commitments.rs:81);
+ * SB200_ERR_ARG for a sharded instance or one with fewer than two constraints. */
+int sb200_snark_encode(const sb200_instance* inst, const sb200_snark_gens* gens, uint8_t** comm_out, size_t* comm_len);
+/* milliseconds of the last sb200_snark_encode: out[0] dense representation, out[1] commitment of comb_ops,
+ * out[2] commitment of comb_mem (CUDA events), out[3] the whole call on the host clock */
+int sb200_last_encode_profile(double out[4]);
+
 /* Measurement helpers (no reference counterpart).
  * sb200_witness_upload places vars in HBM so that a following sb200_nizk_prove(vars32 = NULL, same
  * n_vars) starts with its input resident; sb200_instance_stream returns the cudaStream_t (as an

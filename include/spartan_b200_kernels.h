@@ -58,6 +58,9 @@ int sb200_k_commit_scalar(const sb200_gens* gens, const uint8_t x_canon[32], con
 /* merlin: Transcript::new(label); append_message(mlabel,msg); challenge_bytes(clabel,out)   transcript.rs:13-37 */
 int sb200_k_merlin(const uint8_t* label, size_t ll, const char* mlabel, const uint8_t* msg, size_t ml, const char* clabel,
                    uint8_t* out, size_t n);
+/* MultiSparseMatPolynomialAsDense: comb_ops (16 N scalars) and comb_mem (2 num_mem_cells), canonical 32-byte values
+ * sparse_mlpoly.rs:371-422; dims_out = {N, num_mem_cells}; ops_out / mem_out may be NULL */
+int sb200_k_snark_dense(const sb200_instance* inst, uint64_t dims_out[2], uint8_t* ops_out, uint8_t* mem_out);
 /* kernels launched since the last call to sb200_nizk_prove began (for bench.py's gpu_launches) */
 uint64_t sb200_k_launch_count(void);
 

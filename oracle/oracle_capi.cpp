@@ -201,6 +201,35 @@ int orc_nizk_verify(void* h, const uint8_t* inputs, size_t ni, void* gp, const u
   Transcript tr(std::string((const char*)label, ll));
   return nizk_verify(nz, ((OrcInst*)h)->inst, in, ((OrcGens*)gp)->g, tr) ? 0 : -1;
 }
+// SNARK::encode (lib.rs:321-333).  num_nz_entries is SNARKGens::new's fourth argument (lib.rs:283).  Returns malloc'd
+// bytes: num_cons, num_vars, num_inputs, then bincode of SparseMatPolyCommitment; -1 where the reference would panic.
+// dense_ops / dense_mem (optional): canonical bytes of comb_ops (16 N scalars) / comb_mem (2 num_mem_cells).
+int orc_snark_encode(void* h, size_t num_nz_entries, int threads, uint8_t** out, size_t* out_len, uint8_t* dense_ops,
+                     uint8_t* dense_mem) {
+  try {
+    const Instance& inst = ((OrcInst*)h)->inst;
+    R1CSCommitmentGens gens(inst.num_cons, inst.num_vars, inst.num_inputs, num_nz_entries);
+    SparseAsDense d;
+    R1CSCommitment c = snark_encode(inst, gens, threads, &d);
+    Writer w; w.r1cs_commitment(c);
+    *out = (uint8_t*)malloc(w.b.size());
+    memcpy(*out, w.b.data(), w.b.size());
+    *out_len = w.b.size();
+    if (dense_ops) for (size_t i = 0; i < d.comb_ops.size(); i++) fl_to_bytes(d.comb_ops[i], dense_ops + 32 * i);
+    if (dense_mem) for (size_t i = 0; i < d.comb_mem.size(); i++) fl_to_bytes(d.comb_mem[i], dense_mem + 32 * i);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
+// the dense representation alone (no commitments): sizes out[0] = N, out[1] = num_mem_cells
+int orc_snark_dense(void* h, uint64_t out2[2], uint8_t* dense_ops, uint8_t* dense_mem) {
+  try {
+    SparseAsDense d = sparse_to_dense(((OrcInst*)h)->inst);
+    out2[0] = d.N; out2[1] = d.num_mem_cells;
+    if (dense_ops) for (size_t i = 0; i < d.comb_ops.size(); i++) fl_to_bytes(d.comb_ops[i], dense_ops + 32 * i);
+    if (dense_mem) for (size_t i = 0; i < d.comb_mem.size(); i++) fl_to_bytes(d.comb_mem[i], dense_mem + 32 * i);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
 void orc_free(void* p) { free(p); }
 
 }  // extern "C"

@@ -875,6 +875,122 @@ static inline bool nizk_verify(const NIZK& nz, const Instance& inst, const FlVec
   }
 }
 
+// ------------------------------------------------ SNARK::encode (computation commitment)
+// The public, deterministic half of SNARK mode: lib.rs:321-333 -> R1CSInstance::commit
+// r1csinstance.rs:285-297 -> SparseMatPolynomial::multi_commit sparse_mlpoly.rs:485-506.  No randomness, no transcript.
+struct SparseMatPolyCommitment {  // sparse_mlpoly.rs:330-337
+  size_t batch_size, num_ops, num_mem_cells;
+  std::vector<CPt> comm_comb_ops, comm_comb_mem;
+};
+struct R1CSCommitment {  // r1csinstance.rs:46-51
+  size_t num_cons, num_vars, num_inputs;
+  SparseMatPolyCommitment comm;
+};
+// the dense representation the commitment is taken over (MultiSparseMatPolynomialAsDense, sparse_mlpoly.rs:286-293)
+struct SparseAsDense {
+  size_t N, num_mem_cells;
+  FlVec comb_ops, comb_mem;
+};
+static inline size_t next_pow2(size_t n) {  // usize::next_power_of_two (0 -> 1)
+  size_t p = 1;
+  while (p < n) p <<= 1;
+  return p;
+}
+// DensePolynomial::from_usize uses Scalar::from(u64) = [val,0,0,0] * R2 (scalar/ristretto255.rs:213-217): fl_from_u64, fl.hpp
+// AddrTimestamps::new, sparse_mlpoly.rs:233-266: one audit counter per memory cell, carried across the three matrices
+static inline void addr_timestamps(size_t num_cells, size_t num_ops, const std::vector<size_t> ops_addr[3],
+                                   std::vector<size_t> read_ts[3], std::vector<size_t>& audit_ts) {
+  audit_ts.assign(num_cells, 0);
+  for (int m = 0; m < 3; m++) {
+    if (ops_addr[m].size() != num_ops) throw std::runtime_error("assert_eq!(item.len(), num_ops)");
+    read_ts[m].assign(num_ops, 0);
+    for (size_t i = 0; i < num_ops; i++) {
+      size_t addr = ops_addr[m][i];
+      if (addr >= num_cells) throw std::runtime_error("assert!(addr < num_cells)");
+      size_t r_ts = audit_ts[addr];
+      read_ts[m][i] = r_ts;
+      audit_ts[addr] = r_ts + 1;
+    }
+  }
+}
+// SparseMatPolynomial::multi_sparse_to_dense_rep, sparse_mlpoly.rs:371-422 (+ sparse_to_dense_vecs :353-369,
+// DensePolynomial::merge dense_mlpoly.rs:256-269, from_usize :271-277)
+static inline SparseAsDense sparse_to_dense(const Instance& inst) {
+  SparseAsDense d;
+  size_t N = 0;
+  for (int m = 0; m < 3; m++) N = std::max(N, next_pow2(inst.M[m].size()));
+  N = next_pow2(N);
+  d.N = N;
+  size_t nvx = ilog2(inst.num_cons), nvy = ilog2(2 * inst.num_vars);  // r1csinstance.rs:100-101
+  d.num_mem_cells = size_t(1) << std::max(nvx, nvy);
+  std::vector<size_t> rows[3], cols[3], rts[3], cts[3], raudit, caudit;
+  FlVec val[3];
+  for (int m = 0; m < 3; m++) {
+    rows[m].assign(N, 0); cols[m].assign(N, 0); val[m].assign(N, fl_zero());
+    for (size_t i = 0; i < inst.M[m].size(); i++) {
+      rows[m][i] = inst.M[m][i].row; cols[m][i] = inst.M[m][i].col; val[m][i] = inst.M[m][i].val;
+    }
+  }
+  addr_timestamps(d.num_mem_cells, N, rows, rts, raudit);
+  addr_timestamps(d.num_mem_cells, N, cols, cts, caudit);
+  // comb_ops = row.ops_addr ++ row.read_ts ++ col.ops_addr ++ col.read_ts ++ val, zero-padded to a power of two
+  auto put = [&](const std::vector<size_t>& v) { for (size_t x : v) d.comb_ops.push_back(fl_from_u64(x)); };
+  for (int m = 0; m < 3; m++) put(rows[m]);
+  for (int m = 0; m < 3; m++) put(rts[m]);
+  for (int m = 0; m < 3; m++) put(cols[m]);
+  for (int m = 0; m < 3; m++) put(cts[m]);
+  for (int m = 0; m < 3; m++) d.comb_ops.insert(d.comb_ops.end(), val[m].begin(), val[m].end());
+  d.comb_ops.resize(next_pow2(d.comb_ops.size()), fl_zero());
+  // comb_mem = row.audit_ts extended by col.audit_ts (DensePolynomial::extend, dense_mlpoly.rs:245-254)
+  for (size_t x : raudit) d.comb_mem.push_back(fl_from_u64(x));
+  for (size_t x : caudit) d.comb_mem.push_back(fl_from_u64(x));
+  return d;
+}
+// SparseMatPolyCommitmentGens::new, sparse_mlpoly.rs:301-327: the three generator sets read the same SHAKE stream
+// (same label), so each is a prefix of the longest; only gens_ops and gens_mem are used by encode.
+struct R1CSCommitmentGens {  // r1csinstance.rs:25-44
+  size_t num_vars_ops, num_vars_mem, num_vars_derefs;
+  MultiCommitGens ops_n, mem_n;
+  R1CSCommitmentGens(size_t num_cons, size_t num_vars, size_t num_inputs, size_t num_nz_entries,
+                     const std::string& label = "gens_r1cs_eval") {
+    if (!(num_inputs < num_vars)) throw std::runtime_error("assert!(num_inputs < num_vars)");
+    size_t nvx = ilog2(num_cons), nvy = ilog2(2 * num_vars), batch = 3;
+    num_vars_ops = ilog2(next_pow2(num_nz_entries)) + ilog2(next_pow2(batch * 5));
+    num_vars_mem = std::max(nvx, nvy) + 1;
+    num_vars_derefs = ilog2(next_pow2(num_nz_entries)) + ilog2(next_pow2(batch * 2));
+    auto poly_gens = [&](size_t nv) {  // PolyCommitmentGens::new -> DotProductProofGens::new, dense_mlpoly.rs:28-35
+      size_t n = size_t(1) << (nv - nv / 2);
+      MultiCommitGens a, b;
+      MultiCommitGens::make(n + 1, label).split_at(n, a, b);
+      return a;
+    };
+    ops_n = poly_gens(num_vars_ops);
+    mem_n = poly_gens(num_vars_mem);
+  }
+};
+// DensePolynomial::commit(gens, None), dense_mlpoly.rs:178-203: zero blinds; [Scalar]::commit asserts gens_n.n == R
+static inline std::vector<CPt> poly_commit_unblinded(const FlVec& Z, const MultiCommitGens& gn, int threads) {
+  size_t ell = ilog2(Z.size());
+  if ((size_t(1) << ell) != Z.size()) throw std::runtime_error("assert_eq!(n, ell.pow2())");
+  size_t L = size_t(1) << (ell / 2), R = Z.size() / L;
+  if (gn.n != R) throw std::runtime_error("assert_eq!(gens_n.n, self.len())");
+  return poly_commit_rows(Z, FlVec(L, fl_zero()), gn, threads);
+}
+// SNARKGens::new pads num_vars (lib.rs:283-291); R1CSInstance::commit, r1csinstance.rs:285-297
+static inline R1CSCommitment snark_encode(const Instance& inst, const R1CSCommitmentGens& gens, int threads,
+                                          SparseAsDense* dense_out = nullptr) {
+  SparseAsDense d = sparse_to_dense(inst);
+  R1CSCommitment c;
+  c.num_cons = inst.num_cons; c.num_vars = inst.num_vars; c.num_inputs = inst.num_inputs;
+  c.comm.batch_size = 3;
+  c.comm.num_mem_cells = d.num_mem_cells;
+  c.comm.num_ops = d.N;
+  c.comm.comm_comb_ops = poly_commit_unblinded(d.comb_ops, gens.ops_n, threads);
+  c.comm.comm_comb_mem = poly_commit_unblinded(d.comb_mem, gens.mem_n, threads);
+  if (dense_out) *dense_out = std::move(d);
+  return c;
+}
+
 // ------------------------------------------------ bincode 1.3
 struct Writer {
   std::vector<uint8_t> b;
@@ -900,6 +1016,13 @@ struct Writer {
     eq(p.proof_eq_sc_phase2);
   }
   void nizk(const NIZK& n) { r1cs(n.r1cs_sat_proof); fls(n.rx); fls(n.ry); }
+  // R1CSCommitment's own fields (it is not Serialize in the reference), then bincode of the Serialize
+  // SparseMatPolyCommitment in declaration order (sparse_mlpoly.rs:329-337)
+  void r1cs_commitment(const R1CSCommitment& c) {
+    u64(c.num_cons); u64(c.num_vars); u64(c.num_inputs);
+    u64(c.comm.batch_size); u64(c.comm.num_ops); u64(c.comm.num_mem_cells);
+    pts(c.comm.comm_comb_ops); pts(c.comm.comm_comb_mem);
+  }
 };
 struct Reader {
   const uint8_t* p;

@@ -9,6 +9,7 @@ error behaviour:
     Instance.new / is_sat / produce_synthetic_r1cs      lib.rs:115-272
     NIZKGens.new                                        lib.rs:459-477
     NIZK.prove / NIZK.verify                            lib.rs:479-575
+    SNARKGens.new / SNARK.encode                        lib.rs:273-333 (computation commitment only)
     Transcript.new (merlin)                             spartan-zkinterface/src/main.rs:78
 
 All arithmetic happens in the CUDA library; this module only marshals
@@ -19,7 +20,7 @@ table can be checked without a GPU), every compute call raises
 import ctypes as C
 import os
 
-__all__ = ["Assignment", "VarsAssignment", "InputsAssignment", "Instance", "NIZKGens", "NIZK", "Transcript", "R1CSError",
+__all__ = ["Assignment", "VarsAssignment", "InputsAssignment", "Instance", "NIZKGens", "NIZK", "SNARKGens", "SNARK", "ComputationCommitment", "Transcript", "R1CSError",
            "ProofVerifyError", "BackendError", "lib", "LIB_PATH"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -330,3 +331,65 @@ class NIZK:
                 "kernel_launches", "h2d_bytes", "d2h_bytes", "msm_commit_kernel", "sc_cubic_round0_kernel", "exchange",
                 "exchange_calls", "world", "reserved"]
         return dict(zip(keys, list(d)))
+
+
+class SNARKGens:
+    """`SNARKGens::new(num_cons, num_vars, num_inputs, num_nz_entries)` (lib.rs:279-303) -- the generators
+    SNARK::encode reads (`gens_r1cs_eval`) and their window tables in HBM."""
+
+    def __init__(self, num_cons, num_vars, num_inputs, num_nz_entries):
+        self.h = C.c_void_p()
+        _check(lib().sb200_snark_gens_new(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
+                                          C.c_uint64(num_nz_entries), C.byref(self.h)))
+
+    @staticmethod
+    def new(num_cons, num_vars, num_inputs, num_nz_entries):
+        return SNARKGens(num_cons, num_vars, num_inputs, num_nz_entries)
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.sb200_snark_gens_free(self.h)
+            self.h = None
+
+
+class ComputationCommitment:
+    """`ComputationCommitment` (lib.rs:47-50): R1CSCommitment's sizes and the two polynomial commitments of
+    SparseMatPolyCommitment (sparse_mlpoly.rs:329-337).  `bytes` is the library's wire form (include/spartan_b200.h)."""
+
+    def __init__(self, b):
+        import struct
+        self.bytes = b
+        (self.num_cons, self.num_vars, self.num_inputs, self.batch_size, self.num_ops, self.num_mem_cells,
+         n_ops) = struct.unpack_from("<7Q", b, 0)
+        off = 56
+        self.comm_comb_ops = [b[off + 32 * i:off + 32 * i + 32] for i in range(n_ops)]
+        off += 32 * n_ops
+        n_mem = struct.unpack_from("<Q", b, off)[0]
+        off += 8
+        self.comm_comb_mem = [b[off + 32 * i:off + 32 * i + 32] for i in range(n_mem)]
+        if off + 32 * n_mem != len(b):
+            raise ValueError("trailing bytes after the computation commitment")
+
+    def to_bytes(self):
+        return self.bytes
+
+
+class SNARK:
+    """SNARK mode (lib.rs:305-457).  Only the public preprocessing step is built; `prove` / `verify` are not."""
+
+    @staticmethod
+    def encode(inst, gens):
+        """`SNARK::encode(&inst, &gens)` (lib.rs:321-333).  Returns the ComputationCommitment; the decommitment (the dense
+        representation of the matrices) is rebuilt on the device from `inst` whenever it is needed."""
+        out = C.POINTER(C.c_uint8)()
+        n = C.c_size_t(0)
+        _check(lib().sb200_snark_encode(inst.h, gens.h, C.byref(out), C.byref(n)))
+        b = C.string_at(out, n.value)
+        lib().sb200_free(out)
+        return ComputationCommitment(b)
+
+    @staticmethod
+    def last_encode_profile():
+        d = (C.c_double * 4)()
+        lib().sb200_last_encode_profile(d)
+        return dict(zip(["dense_ms", "commit_ops_ms", "commit_mem_ms", "total_ms"], list(d)))

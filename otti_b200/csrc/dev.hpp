@@ -80,6 +80,11 @@ struct Csr {  // three matrices share the layout
   const uint32_t* idx[3];
   const fl_t* val[3];
 };
+// SNARK::encode: the dense representation of the three matrices (sparse_mlpoly.rs:371-422) as canonical integers:
+// comb_ops (16 N scalars) and comb_mem (2 cells).  op_csr / op_csc: position -> op index (stable CSR / CSC).
+cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint32_t nrows, const Csr& csc,
+                          const uint32_t* const op_csc[3], uint32_t ncols, const uint32_t nnz[3], uint32_t N, uint32_t cells,
+                          fl_t* comb_ops, fl_t* comb_mem, cudaStream_t s);
 // y[m][row] = sum val * z[col]                                        (sparse_mlpoly.rs:452-466)
 cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s);
 // out[col] = rA*sum_A e[row]*val + rB*... + rC*...                    (sparse_mlpoly.rs:468-483, r1csproof.rs:268-279)

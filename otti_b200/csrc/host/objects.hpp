@@ -116,6 +116,10 @@ struct Instance {
   int rank = 0, world = 1;
   uint32_t gamma = 0;
   SparseDev csr, csc;
+  // SNARK::encode needs the ops in insertion order: position in the (stable) CSR / CSC -> index of the entry in the
+  // caller's list (world == 1 only).  pad_entries: lib.rs:191-197 appended zero-valued entries, which are not kept.
+  DevBuf<uint32_t> op_csr[3], op_csc[3];
+  bool pad_entries = false;
   mutable Workspace ws;
 };
 

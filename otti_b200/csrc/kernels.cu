@@ -750,6 +750,101 @@ cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, 
   return SB_LAUNCHED();
 }
 
+// ------------------------------------------------------------------ SNARK::encode: dense representation
+// SparseMatPolynomial::multi_sparse_to_dense_rep (sparse_mlpoly.rs:371-422) without the sequential timestamp loop of
+// AddrTimestamps::new (:233-266).  That loop walks the three matrices in order and, per memory cell, counts the
+// accesses so far: the read timestamp of op i of matrix m at address a is (accesses to a by matrices before m) +
+// (rank of i among the ops of m at a, in op order), the audit timestamp the total.  The CSR / CSC of the instance are
+// stable by construction (spartan_b200.cu upload_sparse), so the rank is the position inside the segment, and the op a
+// position came from is kept beside it (Instance::op_csr / op_csc).  Ops past the last entry of a matrix read cell 0.
+// All outputs are canonical integers (the MSM's input form), not Montgomery.
+struct DenseRepArgs {
+  const uint32_t* ptr[3];  // segment starts (rows or columns), nseg + 1 entries
+  const uint32_t* idx[3];  // unused here (the other coordinate), kept for symmetry with Csr
+  const uint32_t* op[3];   // position -> op index within the matrix
+  const fl_t* val[3];      // Montgomery values by position (NULL: do not write the val block)
+  uint32_t nnz[3];
+  uint32_t nseg, N;
+};
+__device__ __forceinline__ fl_t fl_small(uint64_t x) {
+  fl_t r = fl_zero();
+  r.v[0] = (uint32_t)x;
+  r.v[1] = (uint32_t)(x >> 32);
+  return r;
+}
+__device__ __forceinline__ uint32_t seg_count(const DenseRepArgs& a, int m, uint32_t addr) {
+  uint32_t c = addr < a.nseg ? __ldg(a.ptr[m] + addr + 1) - __ldg(a.ptr[m] + addr) : 0u;
+  return addr == 0 ? c + (a.N - a.nnz[m]) : c;
+}
+// audit_ts[addr] for addr < cells                                            sparse_mlpoly.rs:249-252, 262
+__global__ void snark_audit_kernel(DenseRepArgs a, uint32_t cells, fl_t* __restrict__ audit) {
+  for (uint32_t addr = blockIdx.x * blockDim.x + threadIdx.x; addr < cells; addr += gridDim.x * blockDim.x)
+    st_fl(audit + addr, fl_small((uint64_t)seg_count(a, 0, addr) + seg_count(a, 1, addr) + seg_count(a, 2, addr)));
+}
+// grid.y = matrix.  addr_out / ts_out: 3 blocks of N scalars each (ops_addr and read_ts of this orientation);
+// val_out: 3 blocks of N (written when a.val[m] != NULL).
+__global__ void snark_ops_kernel(DenseRepArgs a, fl_t* __restrict__ addr_out, fl_t* __restrict__ ts_out, fl_t* __restrict__ val_out) {
+  const int m = blockIdx.y;
+  const uint32_t nnz = a.nnz[m], N = a.N;
+  const uint32_t* __restrict__ ptr = a.ptr[m];
+  uint32_t before0 = 0;  // accesses to cell 0 by the matrices before m
+  for (int k = 0; k < m; k++) before0 += seg_count(a, k, 0);
+  const uint32_t own0 = a.nseg ? __ldg(ptr + 1) - __ldg(ptr) : 0u;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < N; p += gridDim.x * blockDim.x) {
+    uint32_t i, addr, ts;
+    if (p < nnz) {
+      uint32_t lo = 0, hi = a.nseg;  // the segment holding position p: largest s with ptr[s] <= p
+      while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(ptr + mid) <= p) lo = mid; else hi = mid;
+      }
+      addr = lo;
+      i = __ldg(a.op[m] + p);
+      ts = p - __ldg(ptr + addr);
+      for (int k = 0; k < m; k++) ts += seg_count(a, k, addr);
+      if (a.val[m] != nullptr) st_fl(val_out + (size_t)m * N + i, fl_from_mont(ldg_fl(a.val[m] + p)));
+    } else {  // padding op: reads cell 0 after every real op of this matrix        sparse_mlpoly.rs:353-369
+      i = p;
+      addr = 0;
+      ts = before0 + own0 + (p - nnz);
+      if (a.val[m] != nullptr) st_fl(val_out + (size_t)m * N + i, fl_zero());
+    }
+    st_fl(addr_out + (size_t)m * N + i, fl_small(addr));
+    st_fl(ts_out + (size_t)m * N + i, fl_small(ts));
+  }
+}
+__global__ void fl_fill_zero_kernel(fl_t* __restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) st_fl(out + i, fl_zero());
+}
+cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint32_t nrows, const Csr& csc,
+                          const uint32_t* const op_csc[3], uint32_t ncols, const uint32_t nnz[3], uint32_t N, uint32_t cells,
+                          fl_t* comb_ops, fl_t* comb_mem, cudaStream_t s) {
+  DenseRepArgs r, c;
+  for (int m = 0; m < 3; m++) {
+    r.ptr[m] = csr.ptr[m]; r.idx[m] = csr.idx[m]; r.op[m] = op_csr[m]; r.val[m] = csr.val[m]; r.nnz[m] = nnz[m];
+    c.ptr[m] = csc.ptr[m]; c.idx[m] = csc.idx[m]; c.op[m] = op_csc[m]; c.val[m] = nullptr; c.nnz[m] = nnz[m];
+  }
+  r.nseg = nrows; c.nseg = ncols;
+  r.N = c.N = N;
+  // comb_ops = row addr | row read_ts | col addr | col read_ts | val | zero padding   (5 x 3 blocks of N, then N zeros)
+  dim3 grid(grid_for(N, 256), 3);
+  snark_ops_kernel<<<grid, 256, 0, s>>>(r, comb_ops, comb_ops + (size_t)3 * N, comb_ops + (size_t)12 * N);
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  snark_ops_kernel<<<grid, 256, 0, s>>>(c, comb_ops + (size_t)6 * N, comb_ops + (size_t)9 * N, nullptr);
+  e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  fl_fill_zero_kernel<<<grid_for(N, 256), 256, 0, s>>>(comb_ops + (size_t)15 * N, N);
+  e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(r, cells, comb_mem);
+  e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(c, cells, comb_mem + cells);
+  return SB_LAUNCHED();
+}
+
 // ------------------------------------------------------------------ fixed-base MSM
 __device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {
   niels_t n;

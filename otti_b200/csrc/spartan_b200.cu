@@ -92,16 +92,24 @@ static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint6
         ptr[(key >> sh) + 1]++;
         nnz++;
       }
-      std::vector<uint32_t> idx(nnz);
+      std::vector<uint32_t> idx(nnz), op(g == 1 ? nnz : 0);
       std::vector<Fl> val(nnz);
       for (uint64_t i = 0; i < nseg; i++) ptr[i + 1] += ptr[i];
       std::vector<uint32_t> fill(ptr.begin(), ptr.end() - 1);
+      uint32_t opi = 0;
       for (const CooEntry& e : M[m]) {
+        const uint32_t this_op = opi++;
         uint32_t key = orient == 0 ? e.row : e.col;
         if ((key & (g - 1)) != k) continue;
-        uint32_t at = fill[key >> sh]++;
+        uint32_t at = fill[key >> sh]++;  // stable: entries of a segment keep the caller's order
         idx[at] = orient == 0 ? e.col : e.row;  // the other coordinate stays global
         val[at] = e.val;
+        if (g == 1) op[at] = this_op;
+      }
+      if (g == 1) {
+        DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
+        SB_CUDA(od.alloc(nnz ? nnz : 1));
+        if (nnz) SB_CUDA(cudaMemcpy(od.p, op.data(), nnz * 4, cudaMemcpyHostToDevice));
       }
       SB_CUDA(sd.ptr[m].alloc(nseg + 1));
       SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
@@ -197,7 +205,8 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
       if (col >= num_vars) col += nvp - num_vars;  // 1 and the inputs live in the second half of z, lib.rs:180-181
       M[m].push_back(CooEntry{(uint32_t)row, (uint32_t)col, v});
     }
-    // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product.
+    // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product
+    // (SNARK::encode would see them as ops: Instance::pad_entries makes sb200_snark_encode refuse such an instance).
   }
   uint32_t gamma = 0;
   int rc = shard_check(rank, world, ncp, nvp, gamma);
@@ -208,6 +217,7 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
   inst->num_cons = ncp; inst->num_vars = nvp; inst->num_inputs = num_inputs;
   inst->rank = rank; inst->world = world; inst->gamma = gamma;
   for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].size();
+  inst->pad_entries = num_cons == 0 || num_cons == 1;
   rc = upload_sparse(M, ncp, 2 * nvp, *inst);
   if (rc) { delete inst; return rc; }
   *out = reinterpret_cast<sb200_instance*>(inst);
@@ -787,3 +797,4 @@ int sb200_last_prove_profile(double out[16]) {
 
 #include "verify.inc"
 #include "kernel_hooks.inc"
+#include "snark.inc"

@@ -317,3 +317,25 @@ def nizk_prove(inst, vars_b, inputs_b, gens, label, tape_seed64, threads=1, want
 def nizk_verify(inst, inputs_b, gens, label, proof):
     return lib().orc_nizk_verify(inst.h, _buf(inputs_b), C.c_size_t(len(inputs_b) // 32), gens.h, _buf(label),
                                  C.c_size_t(len(label)), _buf(proof), C.c_size_t(len(proof)))
+
+
+def snark_dense(inst):
+    """(N, num_mem_cells, comb_ops, comb_mem): the dense representation SNARK::encode commits to, canonical bytes."""
+    d = (C.c_uint64 * 2)()
+    if lib().orc_snark_dense(inst.h, d, None, None) != 0:
+        raise RuntimeError("oracle sparse_to_dense panicked")
+    ops, mem = _out(32 * 16 * d[0]), _out(32 * 2 * d[1])
+    lib().orc_snark_dense(inst.h, d, ops, mem)
+    return d[0], d[1], bytes(ops)[:32 * 16 * d[0]], bytes(mem)[:32 * 2 * d[1]]
+
+
+def snark_encode(inst, num_nz_entries, threads=1):
+    """SNARK::encode (lib.rs:321-333): num_cons, num_vars, num_inputs + bincode(SparseMatPolyCommitment)."""
+    out = u8p()
+    n = C.c_size_t(0)
+    rc = lib().orc_snark_encode(inst.h, C.c_size_t(num_nz_entries), threads, C.byref(out), C.byref(n), None, None)
+    if rc != 0:
+        raise RuntimeError("oracle SNARK::encode panicked (an assert of the reference)")
+    b = C.string_at(out, n.value)
+    lib().orc_free(out)
+    return b
