@@ -269,6 +269,17 @@ void sb200_snark_gens_free(sb200_snark_gens* gens);
  * SB200_ERR_ASSERT where the reference asserts (generators made for other sizes, commitments.rs:81);
  * SB200_ERR_ARG for a sharded instance or one with fewer than two constraints. */
 int sb200_snark_encode(const sb200_instance* inst, const sb200_snark_gens* gens, uint8_t** comm_out, size_t* comm_len);
+/* First step of SNARK::prove's R1CSEvalProof (SparseMatPolyEvalProof::prove, sparse_mlpoly.rs:1485-1503, the
+ * "commit_nondet_witness" timer): the eq tables of the equalized point (rx, ry) (:1453-1469), what every op of the
+ * dense representation reads from them (Derefs, :47-62, 268-284, 508-514) and its unblinded commitment
+ * (Derefs::commit, :64-67).  Deterministic given the point.  rx32 / ry32: canonical scalars.
+ * points_out (release with sb200_free): the L compressed points of DerefsCommitment.comm_ops_val, in order;
+ * comb_out: NULL, or a host buffer of next_power_of_two(6 N) x 32 bytes that receives Derefs.comb (canonical),
+ * N = next_power_of_two(num_nz_entries).  sb200_last_encode_profile then reports out[0] = eq tables + dense
+ * representation + gather, out[1] = the commitment.
+ * SB200_ERR_ASSERT where the reference panics (generators made for other sizes; a point shorter than the memory). */
+int sb200_snark_commit_derefs(const sb200_instance* inst, const sb200_snark_gens* gens, const uint8_t* rx32, uint64_t n_rx,
+                              const uint8_t* ry32, uint64_t n_ry, uint8_t** points_out, size_t* points_len, uint8_t* comb_out);
 /* milliseconds of the last sb200_snark_encode: out[0] dense representation, out[1] commitment of comb_ops,
  * out[2] commitment of comb_mem (CUDA events), out[3] the whole call on the host clock */
 int sb200_last_encode_profile(double out[4]);

@@ -230,6 +230,24 @@ int orc_snark_dense(void* h, uint64_t out2[2], uint8_t* dense_ops, uint8_t* dens
     return 0;
   } catch (const std::exception&) { return -1; }
 }
+// commit_nondet_witness step of SparseMatPolyEvalProof::prove: rx / ry canonical scalars; out32: the L compressed
+// points of DerefsCommitment.comm_ops_val (caller sizes it with cap_points; returns L, or -1 on a reference panic);
+// comb_out (optional): canonical bytes of Derefs.comb (8 N scalars)
+long orc_snark_commit_derefs(void* h, size_t num_nz_entries, const uint8_t* rx, size_t nrx, const uint8_t* ry, size_t nry,
+                             int threads, uint8_t* out32, size_t cap_points, uint8_t* comb_out) {
+  try {
+    const Instance& inst = ((OrcInst*)h)->inst;
+    FlVec vx, vy;
+    if (!load_assign(rx, nrx, vx) || !load_assign(ry, nry, vy)) return InvalidScalar;
+    R1CSCommitmentGens gens(inst.num_cons, inst.num_vars, inst.num_inputs, num_nz_entries);
+    FlVec comb;
+    std::vector<CPt> C = snark_commit_derefs(inst, gens, vx, vy, threads, &comb);
+    if (C.size() > cap_points) return -1;
+    for (size_t i = 0; i < C.size(); i++) memcpy(out32 + 32 * i, C[i].b, 32);
+    if (comb_out) for (size_t i = 0; i < comb.size(); i++) fl_to_bytes(comb[i], comb_out + 32 * i);
+    return (long)C.size();
+  } catch (const std::exception&) { return -1; }
+}
 void orc_free(void* p) { free(p); }
 
 }  // extern "C"

@@ -74,3 +74,23 @@ def snark_encode(inst, num_nz_entries, label=b"gens_r1cs_eval"):
     out += struct.pack("<Q", len(c_ops)) + b"".join(c_ops)
     out += struct.pack("<Q", len(c_mem)) + b"".join(c_mem)
     return out, comb_ops, comb_mem
+
+
+def commit_derefs(inst, num_nz_entries, rx, ry, label=b"gens_r1cs_eval"):
+    """The commit_nondet_witness step of SparseMatPolyEvalProof::prove (sparse_mlpoly.rs:1485-1503): equalize (:1453-1469),
+    eq tables, deref (:268-284, :508-514), Derefs::new (:47-62), Derefs::commit (:64-67).  Returns (points, comb)."""
+    rx, ry = list(rx), list(ry)
+    if len(rx) < len(ry):
+        rx = [0] * (len(ry) - len(rx)) + rx
+    if len(ry) < len(rx):
+        ry = [0] * (len(rx) - len(ry)) + ry
+    mem_rx, mem_ry = S.eq_evals(rx), S.eq_evals(ry)
+    mats = (inst.A, inst.B, inst.C)
+    N = next_pow2(max(next_pow2(len(M)) for M in mats))
+    comb = []
+    for k, mem in ((0, mem_rx), (1, mem_ry)):
+        for M in mats:
+            comb += [mem[e[k]] for e in M] + [mem[0]] * (N - len(M))
+    comb += [0] * (next_pow2(len(comb)) - len(comb))
+    nv_derefs = S.log2(next_pow2(num_nz_entries)) + S.log2(next_pow2(3 * 2))  # sparse_mlpoly.rs:315-316
+    return commit_unblinded(comb, poly_gens_n(nv_derefs, label)), comb

@@ -950,7 +950,7 @@ static inline SparseAsDense sparse_to_dense(const Instance& inst) {
 // (same label), so each is a prefix of the longest; only gens_ops and gens_mem are used by encode.
 struct R1CSCommitmentGens {  // r1csinstance.rs:25-44
   size_t num_vars_ops, num_vars_mem, num_vars_derefs;
-  MultiCommitGens ops_n, mem_n;
+  MultiCommitGens ops_n, mem_n, derefs_n;
   R1CSCommitmentGens(size_t num_cons, size_t num_vars, size_t num_inputs, size_t num_nz_entries,
                      const std::string& label = "gens_r1cs_eval") {
     if (!(num_inputs < num_vars)) throw std::runtime_error("assert!(num_inputs < num_vars)");
@@ -966,6 +966,7 @@ struct R1CSCommitmentGens {  // r1csinstance.rs:25-44
     };
     ops_n = poly_gens(num_vars_ops);
     mem_n = poly_gens(num_vars_mem);
+    derefs_n = poly_gens(num_vars_derefs);
   }
 };
 // DensePolynomial::commit(gens, None), dense_mlpoly.rs:178-203: zero blinds; [Scalar]::commit asserts gens_n.n == R
@@ -989,6 +990,34 @@ static inline R1CSCommitment snark_encode(const Instance& inst, const R1CSCommit
   c.comm.comm_comb_mem = poly_commit_unblinded(d.comb_mem, gens.mem_n, threads);
   if (dense_out) *dense_out = std::move(d);
   return c;
+}
+
+// First step of SparseMatPolyEvalProof::prove (sparse_mlpoly.rs:1485-1503, timer "commit_nondet_witness"): the eq
+// tables of the equalized point, the values every op reads from them (AddrTimestamps::deref :268-284,
+// MultiSparseMatPolynomialAsDense::deref :508-514), merged (Derefs::new :47-62) and committed without blinds
+// (Derefs::commit :64-67).  Deterministic given (rx, ry).
+static inline std::vector<CPt> snark_commit_derefs(const Instance& inst, const R1CSCommitmentGens& gens, const FlVec& rx,
+                                                   const FlVec& ry, int threads, FlVec* comb_out = nullptr) {
+  FlVec rxe = rx, rye = ry;  // equalize, :1453-1469: the shorter point is extended with leading zeros
+  if (rxe.size() < rye.size()) rxe.insert(rxe.begin(), rye.size() - rxe.size(), fl_zero());
+  if (rye.size() < rxe.size()) rye.insert(rye.begin(), rxe.size() - rye.size(), fl_zero());
+  FlVec mem_rx = eq_evals(rxe), mem_ry = eq_evals(rye);
+  size_t N = 0;
+  for (int m = 0; m < 3; m++) N = std::max(N, next_pow2(inst.M[m].size()));
+  N = next_pow2(N);
+  FlVec comb;
+  for (int side = 0; side < 2; side++)
+    for (int m = 0; m < 3; m++)
+      for (size_t i = 0; i < N; i++) {
+        size_t addr = i < inst.M[m].size() ? (side == 0 ? inst.M[m][i].row : inst.M[m][i].col) : 0;
+        const FlVec& mem = side == 0 ? mem_rx : mem_ry;
+        if (addr >= mem.size()) throw std::runtime_error("index out of bounds: mem_val[a]");
+        comb.push_back(mem[addr]);
+      }
+  comb.resize(next_pow2(comb.size()), fl_zero());
+  std::vector<CPt> C = poly_commit_unblinded(comb, gens.derefs_n, threads);
+  if (comb_out) *comb_out = std::move(comb);
+  return C;
 }
 
 // ------------------------------------------------ bincode 1.3

@@ -389,6 +389,29 @@ class SNARK:
         return ComputationCommitment(b)
 
     @staticmethod
+    def commit_derefs(inst, gens, rx, ry, want_comb=False):
+        """The `commit_nondet_witness` step of `SparseMatPolyEvalProof::prove` (sparse_mlpoly.rs:1485-1503): `rx`, `ry` are
+        canonical 32-byte scalars concatenated.  Returns the compressed points of `DerefsCommitment.comm_ops_val`
+        (and, with want_comb, `Derefs.comb` as canonical bytes)."""
+        out = C.POINTER(C.c_uint8)()
+        n = C.c_size_t(0)
+        comb = None
+        if want_comb:
+            N = 1
+            d = (C.c_uint64 * 2)()
+            _check(lib().sb200_k_snark_dense(inst.h, d, None, None))
+            N = int(d[0])
+            comb = (C.c_uint8 * (32 * 8 * N))()
+        xp, xk = _ptr(rx)
+        yp, yk = _ptr(ry)
+        _check(lib().sb200_snark_commit_derefs(inst.h, gens.h, xp, C.c_uint64(len(rx) // 32), yp, C.c_uint64(len(ry) // 32),
+                                               C.byref(out), C.byref(n), comb))
+        b = C.string_at(out, n.value)
+        lib().sb200_free(out)
+        pts = [b[i:i + 32] for i in range(0, len(b), 32)]
+        return (pts, bytes(comb)) if want_comb else pts
+
+    @staticmethod
     def last_encode_profile():
         d = (C.c_double * 4)()
         lib().sb200_last_encode_profile(d)

@@ -85,6 +85,8 @@ struct Csr {  // three matrices share the layout
 cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint32_t nrows, const Csr& csc,
                           const uint32_t* const op_csc[3], uint32_t ncols, const uint32_t nnz[3], uint32_t N, uint32_t cells,
                           fl_t* comb_ops, fl_t* comb_mem, cudaStream_t s);
+// Derefs.comb (8 N canonical scalars) from the address blocks of comb_ops and the two eq tables (Montgomery)
+cudaError_t k_snark_deref(const fl_t* comb_ops, const fl_t* mem_rx, const fl_t* mem_ry, uint32_t N, fl_t* out, cudaStream_t s);
 // y[m][row] = sum val * z[col]                                        (sparse_mlpoly.rs:452-466)
 cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s);
 // out[col] = rA*sum_A e[row]*val + rB*... + rC*...                    (sparse_mlpoly.rs:468-483, r1csproof.rs:268-279)

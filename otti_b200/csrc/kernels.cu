@@ -845,6 +845,29 @@ cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint3
   return SB_LAUNCHED();
 }
 
+// Derefs.comb (sparse_mlpoly.rs:47-62, 268-284, 508-514): what every op reads from the eq tables of the evaluation point,
+// row side then column side, three matrices of N ops each, then 2 N zeros.  The addresses are the low words of the
+// address blocks of comb_ops; mem_rx / mem_ry are Montgomery, the output canonical (the MSM's input form).
+__global__ void snark_deref_kernel(const fl_t* __restrict__ comb_ops, const fl_t* __restrict__ mem_rx, const fl_t* __restrict__ mem_ry,
+                                   uint32_t N, fl_t* __restrict__ out) {
+  const size_t total = (size_t)8 * N;
+  for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t blk = (uint32_t)(t / N);
+    fl_t v = fl_zero();
+    if (blk < 6) {
+      const size_t i = t - (size_t)blk * N;
+      const fl_t* addr = comb_ops + (size_t)(blk < 3 ? blk : 3 + blk) * N + i;  // row addr blocks 0..2, col addr blocks 6..8
+      const uint32_t a = __ldg(&addr->v[0]);
+      v = fl_from_mont(ldg_fl((blk < 3 ? mem_rx : mem_ry) + a));
+    }
+    st_fl(out + t, v);
+  }
+}
+cudaError_t k_snark_deref(const fl_t* comb_ops, const fl_t* mem_rx, const fl_t* mem_ry, uint32_t N, fl_t* out, cudaStream_t s) {
+  snark_deref_kernel<<<grid_for((size_t)8 * N, 256), 256, 0, s>>>(comb_ops, mem_rx, mem_ry, N, out);
+  return SB_LAUNCHED();
+}
+
 // ------------------------------------------------------------------ fixed-base MSM
 __device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {
   niels_t n;

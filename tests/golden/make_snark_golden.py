@@ -26,6 +26,13 @@ def finish(case, inst, nz):
     b, ops, mem = K.snark_encode(inst, nz)
     case.update({"num_nz_entries": nz, "commitment": b.hex(), "comb_ops_sha256": digest(ops), "comb_mem_sha256": digest(mem),
                  "comb_ops_len": len(ops), "comb_mem_len": len(mem)})
+    # the point the sat proof would end at: rx over the constraint variables, ry over the 2 num_vars columns
+    rng = random.Random(len(b))
+    rx = [rng.randrange(S.ELL) for _ in range(S.log2(inst.num_cons))]
+    ry = [rng.randrange(S.ELL) for _ in range(S.log2(2 * inst.num_vars))]
+    pts, comb = K.commit_derefs(inst, nz, rx, ry)
+    case.update({"rx": b"".join(S.fl_to_bytes(x) for x in rx).hex(), "ry": b"".join(S.fl_to_bytes(x) for x in ry).hex(),
+                 "derefs_commitment": b"".join(pts).hex(), "derefs_comb_sha256": digest(comb), "derefs_comb_len": len(comb)})
     return case
 
 

@@ -339,3 +339,19 @@ def snark_encode(inst, num_nz_entries, threads=1):
     b = C.string_at(out, n.value)
     lib().orc_free(out)
     return b
+
+
+def snark_commit_derefs(inst, num_nz_entries, rx_canon, ry_canon, threads=1, want_comb=False):
+    """commit_nondet_witness of SparseMatPolyEvalProof::prove (sparse_mlpoly.rs:1485-1503): the compressed points of
+    DerefsCommitment.comm_ops_val (joined), optionally Derefs.comb as canonical bytes."""
+    N = snark_dense(inst)[0]
+    cap = 8 * N
+    out = _out(32 * cap)
+    comb = _out(32 * 8 * N) if want_comb else None
+    lib().orc_snark_commit_derefs.restype = C.c_long
+    k = lib().orc_snark_commit_derefs(inst.h, C.c_size_t(num_nz_entries), _buf(rx_canon), C.c_size_t(len(rx_canon) // 32),
+                                      _buf(ry_canon), C.c_size_t(len(ry_canon) // 32), threads, out, C.c_size_t(cap), comb)
+    if k < 0:
+        raise RuntimeError("oracle commit_derefs panicked (%d)" % k)
+    pts = bytes(out)[:32 * k]
+    return (pts, bytes(comb)) if want_comb else pts

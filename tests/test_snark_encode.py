@@ -53,6 +53,17 @@ def test_oracle_matches_python_restatement(case):
     assert O.snark_encode(inst, case["num_nz_entries"], threads=2).hex() == case["commitment"]
 
 
+@pytest.mark.parametrize("case", GOLDEN, ids=case_id)
+def test_oracle_derefs_match_python_restatement(case):
+    """commit_nondet_witness of SparseMatPolyEvalProof::prove (sparse_mlpoly.rs:1485-1503), incl. equalize when rx and ry
+    differ in length."""
+    inst = oracle_instance(case)
+    pts, comb = O.snark_commit_derefs(inst, case["num_nz_entries"], bytes.fromhex(case["rx"]), bytes.fromhex(case["ry"]),
+                                      threads=2, want_comb=True)
+    assert len(comb) == 32 * case["derefs_comb_len"] and hashlib.sha256(comb).hexdigest() == case["derefs_comb_sha256"]
+    assert pts.hex() == case["derefs_commitment"]
+
+
 def test_oracle_timestamps_are_a_memory_trace():
     """AddrTimestamps::new (sparse_mlpoly.rs:233-266): per cell the read timestamps, taken in op order over the three
     matrices, count 0, 1, 2, ... and the audit timestamp is the number of accesses; padding ops read cell 0."""
@@ -141,6 +152,36 @@ def test_encode_matches_golden(sb, case):
     cc = sb.SNARK.encode(inst, gens)
     assert cc.bytes.hex() == case["commitment"]
     assert sb.SNARK.encode(inst, gens).bytes == cc.bytes  # deterministic (no tape, no transcript)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", GOLDEN, ids=case_id)
+def test_commit_derefs_matches_golden(sb, case):
+    inst, (nc, nv, ni) = product_instance(sb, case)
+    gens = sb.SNARKGens.new(inst.num_cons, nv, ni, case["num_nz_entries"])
+    pts, comb = sb.SNARK.commit_derefs(inst, gens, bytes.fromhex(case["rx"]), bytes.fromhex(case["ry"]), want_comb=True)
+    assert hashlib.sha256(comb).hexdigest() == case["derefs_comb_sha256"]
+    assert b"".join(pts).hex() == case["derefs_commitment"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("s", [10, 16])
+def test_commit_derefs_matches_oracle(sb, s):
+    """Full-size scalars in every term (eq-table values): the commitment kernel's dense case.  2^16 = configs[1]."""
+    from common import canon, rand_scalars
+    n = 1 << s
+    inst = sb.Instance.produce_synthetic_r1cs(n, n, 10, seed=0x0771)[0]
+    oinst = O.Instance.synthetic(n, n, 10, 0x0771)[0]
+    rx, ry = canon(rand_scalars(s, 40 + s)), canon(rand_scalars(s + 1, 50 + s))
+    gens = sb.SNARKGens.new(n, n, 10, n)
+    pts, comb = sb.SNARK.commit_derefs(inst, gens, rx, ry, want_comb=True)
+    opts, ocomb = O.snark_commit_derefs(oinst, n, rx, ry, threads=os.cpu_count() or 1, want_comb=True)
+    assert comb == ocomb
+    assert b"".join(pts) == opts
+    with pytest.raises(AssertionError):  # a point shorter than the memory: mem_val[a] out of bounds in the reference
+        sb.SNARK.commit_derefs(inst, gens, rx[:32 * (s - 1)], ry[:32 * (s - 1)])
+    with pytest.raises(sb.R1CSError):
+        sb.SNARK.commit_derefs(inst, gens, (ELL).to_bytes(32, "little") * s, ry)
 
 
 @pytest.mark.gpu
