@@ -280,6 +280,15 @@ int sb200_snark_encode(const sb200_instance* inst, const sb200_snark_gens* gens,
  * SB200_ERR_ASSERT where the reference panics (generators made for other sizes; a point shorter than the memory). */
 int sb200_snark_commit_derefs(const sb200_instance* inst, const sb200_snark_gens* gens, const uint8_t* rx32, uint64_t n_rx,
                               const uint8_t* ry32, uint64_t n_ry, uint8_t** points_out, size_t* points_len, uint8_t* comb_out);
+/* Second step of SparseMatPolyEvalProof::prove (sparse_mlpoly.rs:1505-1519, the "build_layered_network" timer):
+ * PolyEvalNetwork::new (:652-668) -- the hash layers (build_hash_layer, :531-606) and the product circuits
+ * (product_tree.rs:16-64) of the row and the column side, built in HBM -- reduced to the sixteen values
+ * ProductCircuit::evaluate returns (the claims ProductLayerProof::prove starts from): out16 = row side init, read[0..3),
+ * write[0..3), audit, then the column side, canonical scalars.  r_hash32 / r_multiset32: the two "challenge_r_hash"
+ * challenges (:1507).  sb200_last_encode_profile then reports out[0] = eq tables + dense representation, out[1] = hash
+ * layers, out[2] = product circuits.  SB200_ERR_ASSERT where the reference panics (point / memory size mismatch). */
+int sb200_snark_network_products(const sb200_instance* inst, const uint8_t* rx32, uint64_t n_rx, const uint8_t* ry32, uint64_t n_ry,
+                                 const uint8_t r_hash32[32], const uint8_t r_multiset32[32], uint8_t out16[512]);
 /* milliseconds of the last sb200_snark_encode: out[0] dense representation, out[1] commitment of comb_ops,
  * out[2] commitment of comb_mem (CUDA events), out[3] the whole call on the host clock */
 int sb200_last_encode_profile(double out[4]);

@@ -248,6 +248,22 @@ long orc_snark_commit_derefs(void* h, size_t num_nz_entries, const uint8_t* rx, 
     return (long)C.size();
   } catch (const std::exception&) { return -1; }
 }
+// build_layered_network of SparseMatPolyEvalProof::prove reduced to the 16 product-circuit evaluations
+// (row side: init, read x3, write x3, audit; then the column side).  All scalars canonical.  -1 on a reference panic.
+int orc_snark_network_products(void* h, const uint8_t* rx, size_t nrx, const uint8_t* ry, size_t nry, const uint8_t r_hash[32],
+                               const uint8_t r_multiset[32], uint8_t out16[512]) {
+  try {
+    FlVec vx, vy, rr;
+    uint8_t two[64];
+    memcpy(two, r_hash, 32);
+    memcpy(two + 32, r_multiset, 32);
+    if (!load_assign(rx, nrx, vx) || !load_assign(ry, nry, vy) || !load_assign(two, 2, rr)) return InvalidScalar;
+    Fl out[16];
+    snark_network_products(((OrcInst*)h)->inst, vx, vy, rr[0], rr[1], out);
+    for (int i = 0; i < 16; i++) fl_to_bytes(out[i], out16 + 32 * i);
+    return 0;
+  } catch (const std::exception&) { return -1; }
+}
 void orc_free(void* p) { free(p); }
 
 }  // extern "C"

@@ -94,3 +94,39 @@ def commit_derefs(inst, num_nz_entries, rx, ry, label=b"gens_r1cs_eval"):
     comb += [0] * (next_pow2(len(comb)) - len(comb))
     nv_derefs = S.log2(next_pow2(num_nz_entries)) + S.log2(next_pow2(3 * 2))  # sparse_mlpoly.rs:315-316
     return commit_unblinded(comb, poly_gens_n(nv_derefs, label)), comb
+
+
+def network_products(inst, rx, ry, r_hash, r_multiset):
+    """PolyEvalNetwork::new (sparse_mlpoly.rs:652-668): build_hash_layer (:531-606) and the product circuits
+    (product_tree.rs:16-64) of both sides, reduced to the 16 values ProductCircuit::evaluate returns.  A product circuit
+    multiplies all its inputs, so the product is taken directly (field arithmetic is exact)."""
+    rx, ry = list(rx), list(ry)
+    if len(rx) < len(ry):
+        rx = [0] * (len(ry) - len(rx)) + rx
+    if len(ry) < len(rx):
+        ry = [0] * (len(rx) - len(ry)) + ry
+    mats = (inst.A, inst.B, inst.C)
+    N = next_pow2(max(next_pow2(len(M)) for M in mats))
+    cells = 1 << max(S.log2(inst.num_cons), S.log2(2 * inst.num_vars))
+    q = S.ELL
+    h2 = r_hash * r_hash % q
+
+    def prod(xs):
+        assert len(xs) >= 2
+        p = 1
+        for x in xs:
+            p = p * x % q
+        return p
+
+    out = []
+    for k, mem in ((0, S.eq_evals(rx)), (1, S.eq_evals(ry))):
+        assert len(mem) == cells
+        addrs = [[e[k] for e in M] + [0] * (N - len(M)) for M in mats]
+        read, audit = addr_timestamps(cells, N, addrs)
+        hsh = lambda a, v, ts: (ts * h2 + v * r_hash + a - r_multiset) % q
+        side = [prod([hsh(i, mem[i], 0) for i in range(cells)])]
+        side += [prod([hsh(a, mem[a], t) for a, t in zip(addrs[m], read[m])]) for m in range(3)]
+        side += [prod([hsh(a, mem[a], t + 1) for a, t in zip(addrs[m], read[m])]) for m in range(3)]
+        side.append(prod([hsh(i, mem[i], audit[i]) for i in range(cells)]))
+        out += side
+    return out

@@ -1020,6 +1020,80 @@ static inline std::vector<CPt> snark_commit_derefs(const Instance& inst, const R
   return C;
 }
 
+// PolyEvalNetwork::new (sparse_mlpoly.rs:652-668, timer "build_layered_network"): Layers::new for the row and the
+// column side -- build_hash_layer (:531-606) and one ProductCircuit (product_tree.rs:16-64) per hashed polynomial --
+// reduced to what the proof then claims: ProductCircuit::evaluate of init, read[0..3), write[0..3), audit.
+static inline Fl product_circuit_evaluate(const FlVec& poly) {  // ProductCircuit::new + evaluate, product_tree.rs:35-64
+  if (poly.size() < 2) throw std::runtime_error("ProductCircuit::new of a polynomial with fewer than two entries");
+  size_t num_layers = ilog2(poly.size());
+  FlVec left(poly.begin(), poly.begin() + poly.size() / 2), right(poly.begin() + poly.size() / 2, poly.end());
+  for (size_t i = 0; i + 1 < num_layers; i++) {  // compute_layer, :17-33
+    size_t len = left.size() + right.size();
+    FlVec ol, orr;
+    for (size_t k = 0; k < len / 4; k++) ol.push_back(fl_mul(left[k], right[k]));
+    for (size_t k = len / 4; k < len / 2; k++) orr.push_back(fl_mul(left[k], right[k]));
+    left.swap(ol);
+    right.swap(orr);
+  }
+  return fl_mul(left[0], right[0]);
+}
+// out[8] = init, read[0], read[1], read[2], write[0], write[1], write[2], audit
+static inline void layers_products(const FlVec& eval_table, const std::vector<size_t> addrs[3], const FlVec derefs[3],
+                                   const std::vector<size_t> read_ts[3], const std::vector<size_t>& audit_ts, const Fl& r_hash,
+                                   const Fl& r_multiset_check, Fl out[8]) {
+  const Fl r_hash_sqr = fl_mul(r_hash, r_hash);
+  auto hash = [&](const Fl& addr, const Fl& val, const Fl& ts) {  // ts * r_hash_sqr + val * r_hash + addr, :548-550
+    return fl_add(fl_add(fl_mul(ts, r_hash_sqr), fl_mul(val, r_hash)), addr);
+  };
+  size_t cells = eval_table.size();
+  FlVec init(cells), audit(cells);
+  for (size_t i = 0; i < cells; i++) {
+    init[i] = fl_sub(hash(fl_from_u64(i), eval_table[i], fl_zero()), r_multiset_check);
+    audit[i] = fl_sub(hash(fl_from_u64(i), eval_table[i], fl_from_u64(audit_ts[i])), r_multiset_check);
+  }
+  out[0] = product_circuit_evaluate(init);
+  out[7] = product_circuit_evaluate(audit);
+  for (int m = 0; m < 3; m++) {
+    size_t n = addrs[m].size();
+    FlVec rd(n), wr(n);
+    for (size_t i = 0; i < n; i++) {
+      Fl a = fl_from_u64(addrs[m][i]), ts = fl_from_u64(read_ts[m][i]);
+      rd[i] = fl_sub(hash(a, derefs[m][i], ts), r_multiset_check);
+      wr[i] = fl_sub(hash(a, derefs[m][i], fl_add(ts, fl_one())), r_multiset_check);  // write_ts = read_ts + 1, :592-597
+    }
+    out[1 + m] = product_circuit_evaluate(rd);
+    out[4 + m] = product_circuit_evaluate(wr);
+  }
+}
+// out[16]: the eight products of the row side, then of the column side
+static inline void snark_network_products(const Instance& inst, const FlVec& rx, const FlVec& ry, const Fl& r_hash,
+                                          const Fl& r_multiset_check, Fl out[16]) {
+  FlVec rxe = rx, rye = ry;
+  if (rxe.size() < rye.size()) rxe.insert(rxe.begin(), rye.size() - rxe.size(), fl_zero());
+  if (rye.size() < rxe.size()) rye.insert(rye.begin(), rxe.size() - rye.size(), fl_zero());
+  FlVec mem_rx = eq_evals(rxe), mem_ry = eq_evals(rye);
+  size_t N = 0;
+  for (int m = 0; m < 3; m++) N = std::max(N, next_pow2(inst.M[m].size()));
+  N = next_pow2(N);
+  size_t cells = size_t(1) << std::max(ilog2(inst.num_cons), ilog2(2 * inst.num_vars));
+  if (mem_rx.size() != cells) throw std::runtime_error("assert_eq!(eval_table.len(), audit_ts.len())");
+  for (int side = 0; side < 2; side++) {
+    const FlVec& mem = side == 0 ? mem_rx : mem_ry;
+    std::vector<size_t> addrs[3], rts[3], audit;
+    FlVec derefs[3];
+    for (int m = 0; m < 3; m++) {
+      addrs[m].assign(N, 0);
+      for (size_t i = 0; i < inst.M[m].size(); i++) addrs[m][i] = side == 0 ? inst.M[m][i].row : inst.M[m][i].col;
+    }
+    addr_timestamps(cells, N, addrs, rts, audit);
+    for (int m = 0; m < 3; m++) {
+      derefs[m].resize(N);
+      for (size_t i = 0; i < N; i++) derefs[m][i] = mem[addrs[m][i]];
+    }
+    layers_products(mem, addrs, derefs, rts, audit, r_hash, r_multiset_check, out + 8 * side);
+  }
+}
+
 // ------------------------------------------------ bincode 1.3
 struct Writer {
   std::vector<uint8_t> b;

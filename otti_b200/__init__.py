@@ -412,6 +412,19 @@ class SNARK:
         return (pts, bytes(comb)) if want_comb else pts
 
     @staticmethod
+    def network_products(inst, rx, ry, r_hash, r_multiset):
+        """`PolyEvalNetwork::new` (sparse_mlpoly.rs:652-668) reduced to the 16 `ProductCircuit::evaluate` values: row side
+        init, read x3, write x3, audit, then the column side (canonical 32-byte scalars)."""
+        out = (C.c_uint8 * 512)()
+        xp, xk = _ptr(rx)
+        yp, yk = _ptr(ry)
+        hp, hk = _ptr(r_hash)
+        mp, mk = _ptr(r_multiset)
+        _check(lib().sb200_snark_network_products(inst.h, xp, C.c_uint64(len(rx) // 32), yp, C.c_uint64(len(ry) // 32), hp, mp, out))
+        b = bytes(out)
+        return [b[32 * i:32 * i + 32] for i in range(16)]
+
+    @staticmethod
     def last_encode_profile():
         d = (C.c_double * 4)()
         lib().sb200_last_encode_profile(d)

@@ -87,6 +87,13 @@ cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint3
                           fl_t* comb_ops, fl_t* comb_mem, cudaStream_t s);
 // Derefs.comb (8 N canonical scalars) from the address blocks of comb_ops and the two eq tables (Montgomery)
 cudaError_t k_snark_deref(const fl_t* comb_ops, const fl_t* mem_rx, const fl_t* mem_ry, uint32_t N, fl_t* out, cudaStream_t s);
+// Hash layer of one side of PolyEvalNetwork (sparse_mlpoly.rs:531-606) into layer 0 of eight product-tree buffers:
+// trees[0] = init, [1..3] = read, [4..6] = write, [7] = audit.  mem Montgomery; addr / ts / audit_ts canonical integers.
+cudaError_t k_snark_hash_layer(const fl_t* mem, const fl_t* addr, const fl_t* ts, const fl_t* audit_ts, uint32_t N, uint32_t cells,
+                               fl_t r_hash, fl_t r_hash_sqr, fl_t r_ms, fl_t* const trees[8], cudaStream_t s);
+// ProductCircuit::new + evaluate (product_tree.rs:16-64) of up to 16 circuits: bufs[i] holds 2 lens[i] scalars, layer k
+// (lens[i] >> k entries, Montgomery) at offset 2 len - (2 len >> k); products[i] canonical.  lens are powers of two >= 2.
+cudaError_t k_prod_trees(fl_t* const bufs[], const uint32_t lens[], int ntrees, fl_t* products, cudaStream_t s);
 // y[m][row] = sum val * z[col]                                        (sparse_mlpoly.rs:452-466)
 cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s);
 // out[col] = rA*sum_A e[row]*val + rB*... + rC*...                    (sparse_mlpoly.rs:468-483, r1csproof.rs:268-279)

@@ -868,6 +868,101 @@ cudaError_t k_snark_deref(const fl_t* comb_ops, const fl_t* mem_rx, const fl_t* 
   return SB_LAUNCHED();
 }
 
+// PolyEvalNetwork::new (sparse_mlpoly.rs:652-668): the hash layer (build_hash_layer, :531-606) and the product circuits
+// (product_tree.rs:16-64) of one side.  hash(addr, val, ts) = ts * r_hash^2 + val * r_hash + addr - r_multiset_check.
+// A product circuit's layer k+1 is the element-wise product of the two halves of layer k (left_vec / right_vec ARE those
+// halves), so a tree is one buffer of 2 len scalars: layer k (len >> k entries) at offset 2 len - (2 len >> k).
+// All values Montgomery; addresses and timestamps arrive as the canonical integers of comb_ops / comb_mem.
+__global__ void snark_hash_mem_kernel(const fl_t* __restrict__ mem, const fl_t* __restrict__ audit_ts, uint32_t cells, fl_t r_hash,
+                                      fl_t r_hash_sqr, fl_t r_ms, fl_t* __restrict__ init_out, fl_t* __restrict__ audit_out) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cells; i += gridDim.x * blockDim.x) {
+    const fl_t a = fl_to_mont(fl_small(i));
+    const fl_t base = fl_sub(fl_add(fl_mul(ldg_fl(mem + i), r_hash), a), r_ms);  // ts = 0 at init time
+    st_fl(init_out + i, base);
+    st_fl(audit_out + i, fl_add(fl_mul(fl_to_mont(ldg_fl(audit_ts + i)), r_hash_sqr), base));
+  }
+}
+// grid.y = matrix; addr / ts: 3 blocks of N canonical integers; read_out / write_out: the 3 tree buffers' layer 0
+struct HashOpsOut {
+  fl_t* read[3];
+  fl_t* write[3];
+};
+__global__ void snark_hash_ops_kernel(const fl_t* __restrict__ mem, const fl_t* __restrict__ addr, const fl_t* __restrict__ ts,
+                                      uint32_t N, fl_t r_hash, fl_t r_hash_sqr, fl_t r_ms, HashOpsOut out) {
+  const int m = blockIdx.y;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const fl_t a = ldg_fl(addr + (size_t)m * N + i);
+    const fl_t v = ldg_fl(mem + a.v[0]);  // the value the op reads (Derefs)
+    const fl_t base = fl_sub(fl_add(fl_mul(v, r_hash), fl_to_mont(a)), r_ms);
+    const fl_t rd = fl_add(fl_mul(fl_to_mont(ldg_fl(ts + (size_t)m * N + i)), r_hash_sqr), base);
+    st_fl(out.read[m] + i, rd);
+    st_fl(out.write[m] + i, fl_add(rd, r_hash_sqr));  // write_ts = read_ts + 1
+  }
+}
+static constexpr int kMaxTrees = 16;
+struct ProdTrees {
+  fl_t* buf[kMaxTrees];
+  uint32_t len[kMaxTrees];
+};
+__device__ __forceinline__ size_t tree_off(uint32_t len, uint32_t k) { return 2 * (size_t)len - ((2 * (size_t)len) >> k); }
+// layer k -> k + 1 of every tree that still has more than `tail` entries in layer k (grid.y = tree)
+__global__ void prod_layer_kernel(ProdTrees t, uint32_t k, uint32_t tail) {
+  const uint32_t len = t.len[blockIdx.y], cur = len >> k;
+  if (cur <= tail) return;
+  const uint32_t h = cur >> 1;
+  const fl_t* __restrict__ in = t.buf[blockIdx.y] + tree_off(len, k);
+  fl_t* __restrict__ out = t.buf[blockIdx.y] + tree_off(len, k + 1);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < h; i += gridDim.x * blockDim.x)
+    st_fl(out + i, fl_mul(ld_fl(in + i), ld_fl(in + h + i)));
+}
+// the remaining layers (at most `tail` = 2 blockDim.x entries) of one tree per block; products[tree] canonical
+__global__ void __launch_bounds__(512) prod_tail_kernel(ProdTrees t, uint32_t tail, fl_t* __restrict__ products) {
+  const uint32_t len = t.len[blockIdx.x];
+  uint32_t k = 0;
+  while ((len >> k) > tail) k++;
+  fl_t* buf = t.buf[blockIdx.x];
+  for (uint32_t cur = len >> k; cur > 1; cur >>= 1, k++) {
+    const uint32_t h = cur >> 1;
+    const fl_t* in = buf + tree_off(len, k);
+    fl_t* out = buf + tree_off(len, k + 1);
+    for (uint32_t i = threadIdx.x; i < h; i += blockDim.x) st_fl(out + i, fl_mul(ld_fl(in + i), ld_fl(in + h + i)));
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) st_fl(products + blockIdx.x, fl_from_mont(ld_fl(buf + tree_off(len, k))));
+}
+// one side: trees[0] = init, [1..3] = read, [4..6] = write, [7] = audit (buffers of 2 len scalars, layer 0 written here)
+cudaError_t k_snark_hash_layer(const fl_t* mem, const fl_t* addr, const fl_t* ts, const fl_t* audit_ts, uint32_t N, uint32_t cells,
+                               fl_t r_hash, fl_t r_hash_sqr, fl_t r_ms, fl_t* const trees[8], cudaStream_t s) {
+  snark_hash_mem_kernel<<<grid_for(cells, 256), 256, 0, s>>>(mem, audit_ts, cells, r_hash, r_hash_sqr, r_ms, trees[0], trees[7]);
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  HashOpsOut o;
+  for (int m = 0; m < 3; m++) { o.read[m] = trees[1 + m]; o.write[m] = trees[4 + m]; }
+  dim3 grid(grid_for(N, 256), 3);
+  snark_hash_ops_kernel<<<grid, 256, 0, s>>>(mem, addr, ts, N, r_hash, r_hash_sqr, r_ms, o);
+  return SB_LAUNCHED();
+}
+// ntrees <= 16 product circuits at once; products[ntrees] canonical
+cudaError_t k_prod_trees(fl_t* const bufs[], const uint32_t lens[], int ntrees, fl_t* products, cudaStream_t s) {
+  if (ntrees < 1 || ntrees > kMaxTrees) return cudaErrorInvalidValue;
+  ProdTrees t;
+  uint32_t maxlen = 0;
+  for (int i = 0; i < kMaxTrees; i++) {
+    t.buf[i] = i < ntrees ? bufs[i] : nullptr;
+    t.len[i] = i < ntrees ? lens[i] : 0;
+    maxlen = t.len[i] > maxlen ? t.len[i] : maxlen;
+  }
+  const uint32_t tail = 1024;
+  for (uint32_t k = 0; (maxlen >> k) > tail; k++) {
+    dim3 grid(grid_for((maxlen >> k) / 2, 256, 4), ntrees);
+    prod_layer_kernel<<<grid, 256, 0, s>>>(t, k, tail);
+    cudaError_t e = SB_LAUNCHED();
+    if (e != cudaSuccess) return e;
+  }
+  prod_tail_kernel<<<ntrees, 512, 0, s>>>(t, tail, products);
+  return SB_LAUNCHED();
+}
+
 // ------------------------------------------------------------------ fixed-base MSM
 __device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {
   niels_t n;

@@ -33,6 +33,10 @@ def finish(case, inst, nz):
     pts, comb = K.commit_derefs(inst, nz, rx, ry)
     case.update({"rx": b"".join(S.fl_to_bytes(x) for x in rx).hex(), "ry": b"".join(S.fl_to_bytes(x) for x in ry).hex(),
                  "derefs_commitment": b"".join(pts).hex(), "derefs_comb_sha256": digest(comb), "derefs_comb_len": len(comb)})
+    rh, rm = rng.randrange(S.ELL), rng.randrange(S.ELL)
+    prods = K.network_products(inst, rx, ry, rh, rm)
+    case.update({"r_hash": S.fl_to_bytes(rh).hex(), "r_multiset_check": S.fl_to_bytes(rm).hex(),
+                 "network_products": [S.fl_to_bytes(x).hex() for x in prods]})
     return case
 
 

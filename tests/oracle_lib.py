@@ -355,3 +355,15 @@ def snark_commit_derefs(inst, num_nz_entries, rx_canon, ry_canon, threads=1, wan
         raise RuntimeError("oracle commit_derefs panicked (%d)" % k)
     pts = bytes(out)[:32 * k]
     return (pts, bytes(comb)) if want_comb else pts
+
+
+def snark_network_products(inst, rx_canon, ry_canon, r_hash_canon, r_multiset_canon):
+    """PolyEvalNetwork::new (sparse_mlpoly.rs:652-668) reduced to the 16 ProductCircuit::evaluate values (canonical):
+    row side init, read x3, write x3, audit, then the column side."""
+    out = _out(512)
+    rc = lib().orc_snark_network_products(inst.h, _buf(rx_canon), C.c_size_t(len(rx_canon) // 32), _buf(ry_canon),
+                                          C.c_size_t(len(ry_canon) // 32), _buf(r_hash_canon), _buf(r_multiset_canon), out)
+    if rc != 0:
+        raise RuntimeError("oracle network products failed: %d" % rc)
+    b = bytes(out)
+    return [b[32 * i:32 * i + 32] for i in range(16)]

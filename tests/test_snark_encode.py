@@ -64,6 +64,27 @@ def test_oracle_derefs_match_python_restatement(case):
     assert pts.hex() == case["derefs_commitment"]
 
 
+def multiset_identity_holds(prods):
+    """hashed_write_set == hashed_read_set (sparse_mlpoly.rs:631-643): init * prod(write) == prod(read) * audit."""
+    v = [int.from_bytes(p, "little") for p in prods]
+    for s0 in (0, 8):
+        lhs = v[s0] * v[s0 + 4] * v[s0 + 5] * v[s0 + 6] % ELL
+        rhs = v[s0 + 1] * v[s0 + 2] * v[s0 + 3] * v[s0 + 7] % ELL
+        if lhs != rhs:
+            return False
+    return True
+
+
+@pytest.mark.parametrize("case", GOLDEN, ids=case_id)
+def test_oracle_network_products_match_python_restatement(case):
+    """PolyEvalNetwork::new (sparse_mlpoly.rs:652-668): hash layers + product circuits, as ProductCircuit::evaluate values."""
+    inst = oracle_instance(case)
+    got = O.snark_network_products(inst, bytes.fromhex(case["rx"]), bytes.fromhex(case["ry"]), bytes.fromhex(case["r_hash"]),
+                                   bytes.fromhex(case["r_multiset_check"]))
+    assert [g.hex() for g in got] == case["network_products"]
+    assert multiset_identity_holds(got)
+
+
 def test_oracle_timestamps_are_a_memory_trace():
     """AddrTimestamps::new (sparse_mlpoly.rs:233-266): per cell the read timestamps, taken in op order over the three
     matrices, count 0, 1, 2, ... and the audit timestamp is the number of accesses; padding ops read cell 0."""
@@ -182,6 +203,47 @@ def test_commit_derefs_matches_oracle(sb, s):
         sb.SNARK.commit_derefs(inst, gens, rx[:32 * (s - 1)], ry[:32 * (s - 1)])
     with pytest.raises(sb.R1CSError):
         sb.SNARK.commit_derefs(inst, gens, (ELL).to_bytes(32, "little") * s, ry)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", GOLDEN, ids=case_id)
+def test_network_products_match_golden(sb, case):
+    inst, _ = product_instance(sb, case)
+    got = sb.SNARK.network_products(inst, bytes.fromhex(case["rx"]), bytes.fromhex(case["ry"]), bytes.fromhex(case["r_hash"]),
+                                    bytes.fromhex(case["r_multiset_check"]))
+    assert [g.hex() for g in got] == case["network_products"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("s", [10, 13, 16])
+def test_network_products_match_oracle(sb, s):
+    """Sizes on both sides of the single-block tail of the product trees; 2^16 = configs[1]."""
+    from common import canon, rand_scalars
+    n = 1 << s
+    inst = sb.Instance.produce_synthetic_r1cs(n, n, 10, seed=0x0771)[0]
+    oinst = O.Instance.synthetic(n, n, 10, 0x0771)[0]
+    rx, ry = canon(rand_scalars(s, 60 + s)), canon(rand_scalars(s + 1, 70 + s))
+    rh, rm = canon(rand_scalars(1, 80 + s)), canon(rand_scalars(1, 90 + s))
+    got = sb.SNARK.network_products(inst, rx, ry, rh, rm)
+    assert got == O.snark_network_products(oinst, rx, ry, rh, rm)
+    assert multiset_identity_holds(got)
+    with pytest.raises(AssertionError):  # eval_table.len() != audit_ts.len()
+        sb.SNARK.network_products(inst, rx, ry[:32 * s], rh, rm)
+
+
+@pytest.mark.gpu
+def test_network_products_full_size_property(sb):
+    """2^20 (the README's SNARK profile size), Otti-like unequal matrices are covered above: here only the size-independent
+    property -- the memory-checking multiset identity init * prod(write) == prod(read) * audit on both sides."""
+    from common import canon, rand_scalars
+    s = 20
+    n = 1 << s
+    inst = sb.Instance.produce_synthetic_r1cs(n, n, 10, seed=0x0771)[0]
+    got = sb.SNARK.network_products(inst, canon(rand_scalars(s, 1)), canon(rand_scalars(s + 1, 2)), canon(rand_scalars(1, 3)),
+                                    canon(rand_scalars(1, 4)))
+    assert multiset_identity_holds(got)
+    # in the synthetic instance op i of A, B and C all touch row i, so on the row side write[A] == read[B], write[B] == read[C]
+    assert got[4] == got[2] and got[5] == got[3] and len(set(got)) == 14
 
 
 @pytest.mark.gpu
