@@ -41,10 +41,43 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log-size", type=int, default=16, help="log2 of constraints = vars (configs[1] = 16)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-snark", action="store_true", help="skip the SNARK-mode side measurements (N = 1 only)")
     ap.add_argument("--shard-log-size", type=int, default=22,
                     help="N > 1: log2 size of the ONE proof additionally sharded over all N GPUs (configs[4]); 0 = skip")
     ap.add_argument("--exchange", default="shm", choices=["shm", "nccl"], help="exchange hook of the sharded proof")
     return ap.parse_args()
+
+
+def snark_side_measurements(sb, inst, n, s):
+    """The parts of SNARK mode that are built, on the bench's own instance, outside the timed region
+    of the headline metric: whole-call milliseconds (best of 3 after one warm-up) of SNARK::encode, of the
+    commit_nondet_witness step and of the build_layered_network step of SNARK::prove.  Never fails the bench line."""
+    try:
+        import random
+        rng = random.Random(s)
+        ell = 2**252 + 27742317777372353535851937790883648493
+        sc = lambda k: b"".join(rng.randrange(ell).to_bytes(32, "little") for _ in range(k))
+        t0 = time.perf_counter()
+        gens = sb.SNARKGens.new(n, n, NUM_INPUTS, n)
+        out = {"workload": "synthetic R1CS 2^%d (the bench instance), instance resident" % s,
+               "gens_build_s_untimed": round(time.perf_counter() - t0, 3)}
+        rx, ry, rh, rm = sc(s), sc(s + 1), sc(1), sc(1)
+        calls = {"encode_ms": lambda: sb.SNARK.encode(inst, gens),
+                 "commit_nondet_witness_ms": lambda: sb.SNARK.commit_derefs(inst, gens, rx, ry),
+                 "build_layered_network_ms": lambda: sb.SNARK.network_products(inst, rx, ry, rh, rm)}
+        for key, fn in calls.items():
+            best = None
+            for _ in range(4):
+                fn()
+                p = sb.SNARK.last_encode_profile()
+                best = p if best is None or p["total_ms"] < best["total_ms"] else best
+            out[key] = round(best["total_ms"], 3)
+            out[key.replace("_ms", "_device_ms")] = round(best["dense_ms"] + best["commit_ops_ms"] + best["commit_mem_ms"], 3)
+        out["published_reference"] = {"encode_s": 14.26, "commit_nondet_witness_s": 14.45, "build_layered_network_s": 3.44,
+                                      "note": "Spartan/README.md:305-345, 2^20, 1 core (other hardware)"}
+        return out
+    except Exception as e:  # a side measurement must not cost the headline line
+        return {"error": "%s: %s" % (type(e).__name__, e)}
 
 
 def host_threads():
@@ -393,6 +426,8 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
     }
+    if world == 1 and not args.no_snark and s <= 20:
+        line["snark_mode"] = snark_side_measurements(sb, inst, n, s)
     if per_rank is not None:
         line["per_rank"] = per_rank
     if sharded is not None:
