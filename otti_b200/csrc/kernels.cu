@@ -1016,15 +1016,16 @@ static __device__ __noinline__ ge_t ge_add_quad(ge_t p, ge_t q) {
   // first half: role 0: A = (Y1-X1)(Y2-X2), 1: B = (Y1+X1)(Y2+X2), 2: D = 2 Z1 Z2, 3: C = 2d T1 T2
   fp_t a = role == 0 ? fp_sub(p.Y, p.X) : role == 1 ? fp_add(p.Y, p.X) : role == 2 ? p.Z : p.T;
   fp_t b = role == 0 ? fp_sub(q.Y, q.X) : role == 1 ? fp_add(q.Y, q.X) : role == 2 ? q.Z : q.T;
-  fp_t m = fp_mul_call(a, b);
-  m = fp_mul_call(m, fp_sel(role == 3, fp_2d(), fp_one()));
+  // products inlined: through a call a dependent product costs a lone warp 559 cycles instead of 467 (tools/microbench/latency_bench.cu)
+  fp_t m = fp_mul(a, b);
+  m = fp_mul(m, fp_sel(role == 3, fp_2d(), fp_one()));
   m = fp_sel(role == 2, fp_add(m, m), m);
   const fp_t A = shfl_fp(m, base), B = shfl_fp(m, base + 1), D = shfl_fp(m, base + 2), C = shfl_fp(m, base + 3);
   const fp_t E = fp_sub(B, A), Fv = fp_sub(D, C), G = fp_add(D, C), H = fp_add(B, A);
   // second half: role 0: X = E F, 1: Y = G H, 2: Z = F G, 3: T = E H
   a = fp_sel((role & 1) == 0, fp_sel(role == 0, E, Fv), fp_sel(role == 1, G, E));
   b = fp_sel((role & 1) == 0, fp_sel(role == 0, Fv, G), H);
-  m = fp_mul_call(a, b);
+  m = fp_mul(a, b);
   ge_t r;
   r.X = shfl_fp(m, base); r.Y = shfl_fp(m, base + 1); r.Z = shfl_fp(m, base + 2); r.T = shfl_fp(m, base + 3);
   return r;
