@@ -276,6 +276,12 @@ struct FpCall {
   static __device__ __forceinline__ fp_t mul(const fp_t& a, const fp_t& b) { return fp_mul_call(a, b); }
   static __device__ __forceinline__ fp_t sqr(const fp_t& a) { return fp_mul_call(a, a); }
 };
+// products through the call, squarings inlined: the squarings of an inversion chain sit in a handful of loops (small
+// code), and a lone warp pays 92 of 559 cycles per dependent product for the call (tools/microbench/latency_bench.cu)
+struct FpSqrInl {
+  static __device__ __forceinline__ fp_t mul(const fp_t& a, const fp_t& b) { return fp_mul_call(a, b); }
+  static __device__ __forceinline__ fp_t sqr(const fp_t& a) { return fp_mul(a, a); }
+};
 #endif
 
 template <class F>

@@ -1145,7 +1145,7 @@ __global__ void __launch_bounds__(32 * kFinishWarps) msm_finish_kernel(const ge_
   for (uint32_t i = nh + ((lane + 32 - (nh & 31)) & 31); i < items; i += 32) acc = ge_add_call(acc, partial[(size_t)row * nsplit + (i - nh)]);
   acc = warp_sum_ge_n(acc, items < 32 ? items : 32);
   uint32_t w[8];
-  ge_compress_t<FpCall>(acc, w);
+  ge_compress_t<FpSqrInl>(acc, w);
   if (lane == 0) {
     uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
     o[0] = make_uint4(w[0], w[1], w[2], w[3]);
