@@ -172,7 +172,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": "constraints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_sharded(args, sb, torch, dist, rank, world, local_rank, flush_l2, barrier):
@@ -252,7 +252,30 @@ def run_sharded(args, sb, torch, dist, rank, world, local_rank, flush_l2, barrie
     }
 
 
+_OUT_FD = None
+
+
+def claim_stdout():
+    """Keep the process's stdout for the ONE JSON line: everything else that writes to file descriptor 1 (NCCL prints its
+    version banner there from C, whatever NCCL_DEBUG_FILE says) goes to stderr from here on."""
+    global _OUT_FD
+    if _OUT_FD is None:
+        sys.stdout.flush()
+        _OUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _OUT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_OUT_FD, data)
+
+
 def main():
+    claim_stdout()
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -432,7 +455,7 @@ def main():
         line["per_rank"] = per_rank
     if sharded is not None:
         line["sharded"] = sharded
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
