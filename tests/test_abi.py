@@ -70,3 +70,19 @@ def test_product_does_not_touch_the_oracle():
     assert not bad, bad
     out = os.popen("ldd %s" % os.path.join(ROOT, "otti_b200", "libspartan_b200.so")).read()
     assert "oracle" not in out
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py's stdout is the one JSON line of the contract, whatever libraries print (the reference arm runs on CPU)."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = out.stdout.splitlines()
+    assert len(lines) == 1 and lines[0].startswith("{")
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["unit"] == "constraints/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
