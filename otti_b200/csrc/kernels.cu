@@ -1079,14 +1079,22 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
     // The entry of window w+1 is requested while window w is added.  Nothing may touch the loaded words before
     // their window comes up (a sign fix-up at load time made every request wait for its own data: 14 % of the
     // kernel's stall samples in profiles/r01_ncu_full_2p22_v5), so the sign of the digit travels to ge_madd.
+    // Windows above the scalar's top bit (plus one for the recoding carry) hold zero digits: a short scalar -- a bit, a
+    // 32-bit word, an address or a timestamp of the SNARK-mode polynomials -- stops after its own windows.
+    uint32_t bitlen = 1;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (kw[i] != 0) bitlen = 32u * i + 32u - (uint32_t)__clz(kw[i]);
+    uint32_t wn = (bitlen - 1) / c + 2;
+    wn = wn < windows ? wn : windows;
     uint32_t carry = 0;
     int32_t d_next = msm_digit(kw, 0, c, carry);
     niels_t e_next;
     if (d_next != 0) e_next = ldg_niels(tb + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1));
-    for (uint32_t w = 0; w < windows; w++) {
+    for (uint32_t w = 0; w < wn; w++) {
       const int32_t d = d_next;
       const niels_t e = e_next;
-      if (w + 1 < windows) {
+      if (w + 1 < wn) {
         d_next = msm_digit(kw, w + 1, c, carry);
         if (d_next != 0) e_next = ldg_niels(tb + ((size_t)(w + 1) << (c - 1)) + ((uint32_t)(d_next < 0 ? -d_next : d_next) - 1));
       }
