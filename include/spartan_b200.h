@@ -103,8 +103,9 @@ typedef struct sb200_comm_vt {
 } sb200_comm_vt;
 
 /* Exchange over a POSIX shared-memory segment for ranks on ONE box (the 8 x B200 node of north_star): fills
- * *out with a hook whose allgather costs ~1 us.  Collective: every rank calls it with the same name, which must
- * be unique to the job (a stale segment of the same name must not exist).  Hosts spanning boxes supply their own
+ * *out with a hook whose allgather costs ~1 us.  Collective: every rank calls it with the same name, which should
+ * be unique to the job.  Rank 0 removes whatever a crashed job left under that name and creates the segment anew; the
+ * other ranks only accept a segment in which rank 0 of THIS call answers them.  Hosts spanning boxes supply their own
  * hook (NCCL / torch.distributed: otti_b200/comm.py). */
 int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out);
 void sb200_comm_shm_close(sb200_comm_vt* comm);
@@ -216,6 +217,13 @@ int sb200_circ_int_to_scalar(const uint8_t* magnitude_le, size_t len, uint8_t ou
  * the reference builds its gens outside the bench loop, benches/nizk.rs:27-39). */
 int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs,
                    sb200_gens** out);
+/* The same with a hint: how many proofs the caller expects to make with these generators.  The window width of the
+ * tables is then chosen to minimise table build + proofs_expected x commitment instead of filling the HBM: a one-shot
+ * caller like spzk, which times NIZKGens::new together with the prove (spartan-zkinterface/src/main.rs:71-85), passes 1
+ * and gets generators in milliseconds.  0 = many (what sb200_gens_new does, unless SB200_PROOFS_EXPECTED is set).
+ * The generators -- and so every proof byte -- do not depend on the hint. */
+int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs,
+                       uint64_t proofs_expected, sb200_gens** out);
 void sb200_gens_free(sb200_gens* gens);
 
 /* NIZK::prove(&inst, vars, &inputs, &gens, &mut transcript) -> NIZK      lib.rs:493-535

@@ -63,6 +63,11 @@ int sb200_k_merlin(const uint8_t* label, size_t ll, const char* mlabel, const ui
 int sb200_k_snark_dense(const sb200_instance* inst, uint64_t dims_out[2], uint8_t* ops_out, uint8_t* mem_out);
 /* kernels launched since the last call to sb200_nizk_prove began (for bench.py's gpu_launches) */
 uint64_t sb200_k_launch_count(void);
+/* Per-kernel device time: while enabled, every kernel launch of the library is bracketed by CUDA events on its stream
+ * (a few microseconds per launch, so never inside a timed region).  sb200_k_kprof_report writes "kernel,launches,total_ms"
+ * lines, longest first, for everything launched since the last report, and clears the records. */
+int sb200_k_kprof_enable(int on);
+int sb200_k_kprof_report(char* out, size_t cap);
 
 #ifdef __cplusplus
 }

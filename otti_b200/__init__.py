@@ -88,6 +88,8 @@ def _ptr(obj):
         return C.c_void_p(obj.ctypes.data), obj
     if isinstance(obj, bytes):  # no copy: the bytes object itself is the keep-alive
         return C.cast(C.c_char_p(obj), C.c_void_p), obj
+    if isinstance(obj, C.Array):  # no copy either
+        return C.cast(obj, C.c_void_p), obj
     b = (C.c_uint8 * max(len(obj), 1)).from_buffer_copy(bytes(obj)) if len(obj) else (C.c_uint8 * 1)()
     return C.cast(b, C.c_void_p), b
 
@@ -256,15 +258,26 @@ class Instance:
 class NIZKGens:
     """`NIZKGens::new(num_cons, num_vars, num_inputs)` (lib.rs:466-477)."""
 
-    def __init__(self, num_cons, num_vars, num_inputs, label=None):
+    def __init__(self, num_cons, num_vars, num_inputs, label=None, proofs_expected=None):
         self.h = C.c_void_p()
         lp, keep = _ptr(label)
-        _check(lib().sb200_gens_new(lp, C.c_size_t(len(label) if label else 0), C.c_uint64(num_cons), C.c_uint64(num_vars),
-                                    C.c_uint64(num_inputs), C.byref(self.h)))
+        if proofs_expected is None:
+            _check(lib().sb200_gens_new(lp, C.c_size_t(len(label) if label else 0), C.c_uint64(num_cons), C.c_uint64(num_vars),
+                                        C.c_uint64(num_inputs), C.byref(self.h)))
+        else:
+            _check(lib().sb200_gens_new_for(lp, C.c_size_t(len(label) if label else 0), C.c_uint64(num_cons),
+                                            C.c_uint64(num_vars), C.c_uint64(num_inputs), C.c_uint64(proofs_expected),
+                                            C.byref(self.h)))
 
     @staticmethod
-    def new(num_cons, num_vars, num_inputs):
-        return NIZKGens(num_cons, num_vars, num_inputs)
+    def new(num_cons, num_vars, num_inputs, proofs_expected=None):
+        """proofs_expected: None / 0 = many proofs (widest window tables that fit the HBM, built once: 0.2-1.2 s);
+        k > 0 = tables sized for k proofs (1: a one-shot caller such as spzk, whose timer covers gens + prove)."""
+        return NIZKGens(num_cons, num_vars, num_inputs, proofs_expected=proofs_expected)
+
+    @property
+    def window_bits(self):
+        return int(lib().sb200_k_gens_window(self.h))
 
     def __del__(self):
         if getattr(self, "h", None) and _lib is not None:

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <string>
+
 #include "fl.cuh"
 
 namespace sb {
@@ -75,10 +77,27 @@ cudaError_t k_eq_table_scaled(const fl_t* r, uint32_t ell, fl_t init, fl_t* out,
 // out[i] = in[i*step + first], i < n
 cudaError_t k_gather_stride(const fl_t* in, size_t n, size_t step, size_t first, fl_t* out, cudaStream_t s);
 
+// Segments (rows of a CSR, columns of a CSC) longer than kLongSeg entries are not walked by one thread: they are cut
+// into chunks of at most kSegChunk entries, a warp sums each chunk (sp_long_kernel), segments of more than
+// kSumInline chunks are then reduced by one warp each (sp_big_kernel), and the thread that owns the segment in the
+// main kernel picks the sum up.  CirC output has such segments: the constant-1 column holds a quarter of all
+// entries, decomposition rows have 32-64 terms.  F_l addition is exact, so the split cannot change a bit.
+static constexpr uint32_t kLongSeg = 16, kSegChunk = 512, kSumInline = 8;
+struct LongSegs {
+  const uint32_t* seg = nullptr;       // [nlong] ids of the long segments, ascending
+  const uint32_t* first = nullptr;     // [nlong + 1] first chunk of each
+  const uint32_t* chunk_lo = nullptr;  // [nchunks] entry range of a chunk
+  const uint32_t* chunk_hi = nullptr;
+  const uint32_t* big = nullptr;       // [nbig] indices into seg[] of the segments with more than kSumInline chunks
+  fl_t* partial = nullptr;             // [nchunks] scratch: chunk sums
+  fl_t* reduced = nullptr;             // [nlong] scratch: sums of the big segments
+  uint32_t nlong = 0, nchunks = 0, nbig = 0;
+};
 struct Csr {  // three matrices share the layout
   const uint32_t* ptr[3];
   const uint32_t* idx[3];
   const fl_t* val[3];
+  LongSegs lg[3];
 };
 // SNARK::encode: the dense representation of the three matrices (sparse_mlpoly.rs:371-422) as canonical integers:
 // comb_ops (16 N scalars) and comb_mem (2 cells).  op_csr / op_csc: position -> op index (stable CSR / CSC).
@@ -139,6 +158,10 @@ cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t*
 // s[g] = from_mont(d * coeff[g]) for g < R                            (nizk/mod.rs:483-490)
 cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s);
 
+// per-kernel device time of every launch while enabled (CUDA events around each launch); report = CSV lines
+// "kernel,launches,total_ms" sorted by time, and clears the records
+void kprof_enable(bool on);
+std::string kprof_report();
 // counter of kernel launches issued through this file (bench.py gpu_launches)
 uint64_t launch_count();
 void launch_count_reset();

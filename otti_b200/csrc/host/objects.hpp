@@ -7,6 +7,7 @@
 
 #include <cstdint>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -53,9 +54,19 @@ struct DevBuf {
 struct SparseDev {  // CSR (by row) or CSC (by column) of the three matrices
   DevBuf<uint32_t> ptr[3], idx[3];
   DevBuf<sb::fl_t> val[3];
+  // long segments (dev.hpp LongSegs): lists built once by upload_sparse, scratch reused by every call on the instance
+  DevBuf<uint32_t> lg_seg[3], lg_first[3], lg_lo[3], lg_hi[3], lg_big[3];
+  DevBuf<sb::fl_t> lg_partial[3], lg_reduced[3];
+  uint32_t nlong[3] = {0, 0, 0}, nchunks[3] = {0, 0, 0}, nbig[3] = {0, 0, 0};
   sb::Csr view() const {
     sb::Csr c;
-    for (int m = 0; m < 3; m++) { c.ptr[m] = ptr[m].p; c.idx[m] = idx[m].p; c.val[m] = val[m].p; }
+    for (int m = 0; m < 3; m++) {
+      c.ptr[m] = ptr[m].p; c.idx[m] = idx[m].p; c.val[m] = val[m].p;
+      sb::LongSegs& l = c.lg[m];
+      l.seg = lg_seg[m].p; l.first = lg_first[m].p; l.chunk_lo = lg_lo[m].p; l.chunk_hi = lg_hi[m].p; l.big = lg_big[m].p;
+      l.partial = lg_partial[m].p; l.reduced = lg_reduced[m].p;
+      l.nlong = nlong[m]; l.nchunks = nchunks[m]; l.nbig = nbig[m];
+    }
     return c;
   }
 };
@@ -121,6 +132,9 @@ struct Instance {
   DevBuf<uint32_t> op_csr[3], op_csc[3];
   bool pad_entries = false;
   mutable Workspace ws;
+  // NIZK::verify / is_sat / prove take `&Instance` in the reference and may be called from several threads; here they
+  // share the workspace, the stream and the mailbox of the handle, so every entry point that touches them locks this.
+  mutable std::mutex mu;
 };
 
 struct Gens {

@@ -12,8 +12,12 @@
 //   k_dot_small        DotProductProofLog::compute_dotproduct      nizk/mod.rs:430-433
 //   k_bullet_step      BulletReductionProof::prove scalar side     nizk/bullet.rs:71-118
 //   msm_fixed          [Scalar]::commit -> vartime_multiscalar_mul commitments.rs:79-84, dense_mlpoly.rs:163-176
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
+#include <mutex>
+#include <string>
+#include <vector>
 
 #include "dev.hpp"
 #include "ge.cuh"
@@ -24,6 +28,65 @@ static std::atomic<uint64_t> g_launches{0};
 uint64_t launch_count() { return g_launches.load(); }
 void launch_count_reset() { g_launches.store(0); }
 #define SB_LAUNCHED() (g_launches.fetch_add(1), cudaGetLastError())
+
+// Per-kernel device time (bench.py: which kernel dominates a step, and for how long): when switched on, every launch
+// of this file is bracketed by two CUDA events on its stream.  Off during every timed region -- the brackets cost a few
+// microseconds per launch; the totals come from a separate profiling pass over the same workload.
+struct KProfRec { const char* name; cudaEvent_t a, b; };
+static std::atomic<int> g_kprof_on{0};
+static std::mutex g_kprof_mu;
+static std::vector<KProfRec> g_kprof_recs;
+static std::vector<cudaEvent_t> g_kprof_free;
+struct KProf {
+  cudaStream_t s_;
+  cudaEvent_t a_ = nullptr, b_ = nullptr;
+  const char* name_;
+  static cudaEvent_t get() {
+    std::lock_guard<std::mutex> lk(g_kprof_mu);
+    if (!g_kprof_free.empty()) { cudaEvent_t e = g_kprof_free.back(); g_kprof_free.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+  }
+  KProf(const char* name, cudaStream_t s) : s_(s), name_(name) {
+    if (!g_kprof_on.load(std::memory_order_relaxed)) return;
+    a_ = get(); b_ = get();
+    cudaEventRecord(a_, s_);
+  }
+  ~KProf() {
+    if (!a_) return;
+    cudaEventRecord(b_, s_);
+    std::lock_guard<std::mutex> lk(g_kprof_mu);
+    g_kprof_recs.push_back(KProfRec{name_, a_, b_});
+  }
+};
+void kprof_enable(bool on) { g_kprof_on.store(on ? 1 : 0); }
+// "name,launches,total_ms\n" per kernel, sorted by total time; clears the records
+std::string kprof_report() {
+  cudaDeviceSynchronize();
+  std::lock_guard<std::mutex> lk(g_kprof_mu);
+  std::vector<std::pair<std::string, std::pair<uint64_t, double>>> tot;
+  for (const KProfRec& r : g_kprof_recs) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, r.a, r.b);
+    size_t i = 0;
+    for (; i < tot.size(); i++) if (tot[i].first == r.name) break;
+    if (i == tot.size()) tot.push_back({r.name, {0, 0.0}});
+    tot[i].second.first++;
+    tot[i].second.second += ms;
+    g_kprof_free.push_back(r.a);
+    g_kprof_free.push_back(r.b);
+  }
+  g_kprof_recs.clear();
+  std::sort(tot.begin(), tot.end(), [](const auto& x, const auto& y) { return x.second.second > y.second.second; });
+  std::string out;
+  char line[256];
+  for (auto& t : tot) {
+    snprintf(line, sizeof line, "%s,%llu,%.6f\n", t.first.c_str(), (unsigned long long)t.second.first, t.second.second);
+    out += line;
+  }
+  return out;
+}
 
 static constexpr int kSMs = 148;  // B200
 
@@ -178,22 +241,22 @@ __global__ void fp_binop_kernel(int op, const fp_t* a, const fp_t* b, fp_t* out,
 }
 cudaError_t k_fp_binop(int op, const fp_t* a, const fp_t* b, fp_t* out, size_t n, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  fp_binop_kernel<<<grid_for(n, 128), 128, 0, s>>>(op, a, b, out, n);
+  { KProf kp_("fp_binop_kernel", s); fp_binop_kernel<<<grid_for(n, 128), 128, 0, s>>>(op, a, b, out, n); }
   return SB_LAUNCHED();
 }
 cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n, flag);
+  { KProf kp_("to_mont_kernel", s); to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n, flag); }
   return SB_LAUNCHED();
 }
 cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  from_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n);
+  { KProf kp_("from_mont_kernel", s); from_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n); }
   return SB_LAUNCHED();
 }
 cudaError_t k_fl_binop(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  fl_binop_kernel<<<grid_for(n, 256), 256, 0, s>>>(op, a, b, out, n);
+  { KProf kp_("fl_binop_kernel", s); fl_binop_kernel<<<grid_for(n, 256), 256, 0, s>>>(op, a, b, out, n); }
   return SB_LAUNCHED();
 }
 
@@ -207,7 +270,7 @@ __global__ void check_sat_kernel(const fl_t* __restrict__ A, const fl_t* __restr
 }
 cudaError_t k_check_sat(const fl_t* A, const fl_t* B, const fl_t* C, size_t n, uint32_t* flag, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  check_sat_kernel<<<grid_for(n, 256), 256, 0, s>>>(A, B, C, n, flag);
+  { KProf kp_("check_sat_kernel", s); check_sat_kernel<<<grid_for(n, 256), 256, 0, s>>>(A, B, C, n, flag); }
   return SB_LAUNCHED();
 }
 
@@ -236,20 +299,20 @@ __global__ void eq_outer_kernel(const fl_t* __restrict__ hi, const fl_t* __restr
 }
 cudaError_t k_eq_table_scaled(const fl_t* r, uint32_t ell, fl_t init, fl_t* out, fl_t* tmp, cudaStream_t s) {
   if (ell <= 8) {
-    eq_small_kernel<<<((1u << ell) + 127) / 128, 128, 0, s>>>(r, ell, init, out);
+    { KProf kp_("eq_small_kernel", s); eq_small_kernel<<<((1u << ell) + 127) / 128, 128, 0, s>>>(r, ell, init, out); }
     return SB_LAUNCHED();
   }
   uint32_t a = ell / 2, b = ell - a;  // high a variables (r[0..a)), low b variables
   fl_t* hi = tmp;
   fl_t* lo = tmp + ((size_t)1 << a);
-  eq_small_kernel<<<((1u << a) + 127) / 128, 128, 0, s>>>(r, a, init, hi);
+  { KProf kp_("eq_small_kernel", s); eq_small_kernel<<<((1u << a) + 127) / 128, 128, 0, s>>>(r, a, init, hi); }
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  eq_small_kernel<<<((1u << b) + 127) / 128, 128, 0, s>>>(r + a, b, fl_one(), lo);
+  { KProf kp_("eq_small_kernel", s); eq_small_kernel<<<((1u << b) + 127) / 128, 128, 0, s>>>(r + a, b, fl_one(), lo); }
   e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
   size_t n = (size_t)1 << ell;
-  eq_outer_kernel<<<grid_for(n, 256), 256, 0, s>>>(hi, lo, b, n, out);
+  { KProf kp_("eq_outer_kernel", s); eq_outer_kernel<<<grid_for(n, 256), 256, 0, s>>>(hi, lo, b, n, out); }
   return SB_LAUNCHED();
 }
 cudaError_t k_eq_table(const fl_t* r, uint32_t ell, fl_t* out, fl_t* tmp, cudaStream_t s) {
@@ -262,49 +325,122 @@ __global__ void gather_stride_kernel(const fl_t* __restrict__ in, size_t n, size
 }
 cudaError_t k_gather_stride(const fl_t* in, size_t n, size_t step, size_t first, fl_t* out, cudaStream_t s) {
   if (!n) return cudaSuccess;
-  gather_stride_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, n, step, first, out);
+  { KProf kp_("gather_stride_kernel", s); gather_stride_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, n, step, first, out); }
   return SB_LAUNCHED();
 }
 
 // ------------------------------------------------------------------ sparse mat-vec
+// R1CS matrices out of a circuit compiler are mostly +1 / -1 (copy constraints, booleanity, bit decompositions):
+// those entries cost an addition instead of a Montgomery product (136 IMAD.WIDE).
+__device__ __forceinline__ fl_t fl_minus_one() {  // l - R
+  fl_t r;
+  r.v[0] = 0xcf5d3ed0u; r.v[1] = 0x812631a5u; r.v[2] = 0x2f79cd65u; r.v[3] = 0x4def9deau;
+  r.v[4] = 0x00000001u; r.v[5] = 0x00000000u; r.v[6] = 0x00000000u; r.v[7] = 0x00000000u;
+  return r;
+}
+__device__ __forceinline__ fl_t coef_times(const fl_t& val, const fl_t& x) {
+  if (fl_eq(val, fl_one())) return x;
+  if (fl_eq(val, fl_minus_one())) return fl_sub(fl_zero(), x);
+  return fl_mul_call(val, x);
+}
+// sum over the entries [k0, k1) of one segment, by the thread that owns the segment: short segments are walked, long
+// ones were summed by sp_long_kernel / sp_big_kernel (dev.hpp LongSegs)
+__device__ __forceinline__ fl_t seg_sum(const uint32_t* __restrict__ idx, const fl_t* __restrict__ val, const LongSegs& lg,
+                                        const fl_t* __restrict__ x, uint32_t seg, uint32_t k0, uint32_t k1) {
+  fl_t acc = fl_zero();
+  if (k1 - k0 <= kLongSeg) {
+    for (uint32_t k = k0; k < k1; k++) acc = fl_add(acc, coef_times(ldg_fl(val + k), ldg_fl(x + __ldg(idx + k))));
+    return acc;
+  }
+  uint32_t lo = 0, hi = lg.nlong;  // position of seg in the ascending list of long segments
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (__ldg(lg.seg + mid) <= seg) lo = mid; else hi = mid;
+  }
+  const uint32_t c0 = __ldg(lg.first + lo), c1 = __ldg(lg.first + lo + 1);
+  if (c1 - c0 > kSumInline) return ldcg_fl(lg.reduced + lo);
+  for (uint32_t c = c0; c < c1; c++) acc = fl_add(acc, ldcg_fl(lg.partial + c));
+  return acc;
+}
+// one warp per chunk of a long segment (grid.y = matrix)
+__global__ void __launch_bounds__(256) sp_long_kernel(Csr mat, const fl_t* __restrict__ x) {
+  const int m = blockIdx.y;
+  const LongSegs& lg = mat.lg[m];
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < lg.nchunks; c += gridDim.x * (blockDim.x >> 5)) {
+    const uint32_t k0 = __ldg(lg.chunk_lo + c), k1 = __ldg(lg.chunk_hi + c);
+    const uint32_t* __restrict__ idx = mat.idx[m];
+    const fl_t* __restrict__ val = mat.val[m];
+    fl_t acc = fl_zero();
+    for (uint32_t k = k0 + lane; k < k1; k += 32) acc = fl_add(acc, coef_times(ldg_fl(val + k), ldg_fl(x + __ldg(idx + k))));
+    acc = warp_sum_fl(acc);
+    if (lane == 0) st_fl(lg.partial + c, acc);
+  }
+}
+// one warp per segment of more than kSumInline chunks: reduced[j] = sum of its chunk sums
+__global__ void __launch_bounds__(256) sp_big_kernel(Csr mat) {
+  const int m = blockIdx.y;
+  const LongSegs& lg = mat.lg[m];
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); b < lg.nbig; b += gridDim.x * (blockDim.x >> 5)) {
+    const uint32_t j = __ldg(lg.big + b), c0 = __ldg(lg.first + j), c1 = __ldg(lg.first + j + 1);
+    fl_t acc = fl_zero();
+    for (uint32_t c = c0 + lane; c < c1; c += 32) acc = fl_add(acc, ldcg_fl(lg.partial + c));
+    acc = warp_sum_fl(acc);
+    if (lane == 0) st_fl(lg.reduced + j, acc);
+  }
+}
+static cudaError_t sp_long_pass(const Csr& mat, const fl_t* x, cudaStream_t s) {
+  uint32_t maxc = 0, maxb = 0;
+  for (int m = 0; m < 3; m++) { maxc = std::max(maxc, mat.lg[m].nchunks); maxb = std::max(maxb, mat.lg[m].nbig); }
+  if (!maxc) return cudaSuccess;
+  dim3 grid(grid_for(maxc, 8, 16), 3);  // 8 chunks per block
+  { KProf kp_("sp_long_kernel", s); sp_long_kernel<<<grid, 256, 0, s>>>(mat, x); }
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess || !maxb) return e;
+  dim3 gridb(grid_for(maxb, 8, 16), 3);
+  { KProf kp_("sp_big_kernel", s); sp_big_kernel<<<gridb, 256, 0, s>>>(mat); }
+  return SB_LAUNCHED();
+}
 __global__ void spmv3_kernel(Csr csr, uint32_t num_rows, const fl_t* __restrict__ z, fl_t* __restrict__ yA,
                              fl_t* __restrict__ yB, fl_t* __restrict__ yC) {
   const int m = blockIdx.y;
   const uint32_t* __restrict__ ptr = csr.ptr[m];
-  const uint32_t* __restrict__ idx = csr.idx[m];
-  const fl_t* __restrict__ val = csr.val[m];
   fl_t* y = m == 0 ? yA : m == 1 ? yB : yC;
   for (uint32_t row = blockIdx.x * blockDim.x + threadIdx.x; row < num_rows; row += gridDim.x * blockDim.x) {
-    uint32_t k0 = __ldg(ptr + row), k1 = __ldg(ptr + row + 1);
-    fl_t acc = fl_zero();
-    for (uint32_t k = k0; k < k1; k++) acc = fl_add(acc, fl_mul(ldg_fl(val + k), ldg_fl(z + __ldg(idx + k))));
-    st_fl(y + row, acc);
+    const uint32_t k0 = __ldg(ptr + row), k1 = __ldg(ptr + row + 1);
+    st_fl(y + row, seg_sum(csr.idx[m], csr.val[m], csr.lg[m], z, row, k0, k1));
   }
 }
 cudaError_t k_spmv3(const Csr& csr, uint32_t num_rows, const fl_t* z, fl_t* yA, fl_t* yB, fl_t* yC, cudaStream_t s) {
+  cudaError_t e = sp_long_pass(csr, z, s);
+  if (e != cudaSuccess) return e;
   dim3 grid(grid_for(num_rows, 128), 3);
-  spmv3_kernel<<<grid, 128, 0, s>>>(csr, num_rows, z, yA, yB, yC);
+  { KProf kp_("spmv3_kernel", s); spmv3_kernel<<<grid, 128, 0, s>>>(csr, num_rows, z, yA, yB, yC); }
   return SB_LAUNCHED();
 }
 __global__ void spmvT3_kernel(Csr csc, uint32_t num_cols, const fl_t* __restrict__ e, fl_t rA, fl_t rB, fl_t rC,
                               fl_t* __restrict__ out) {
   for (uint32_t col = blockIdx.x * blockDim.x + threadIdx.x; col < num_cols; col += gridDim.x * blockDim.x) {
+    // the six segment bounds are requested together; most columns of a padded z are empty in all three matrices
+    uint32_t k0[3], k1[3];
+#pragma unroll
+    for (int m = 0; m < 3; m++) { k0[m] = __ldg(csc.ptr[m] + col); k1[m] = __ldg(csc.ptr[m] + col + 1); }
     fl_t tot = fl_zero();
 #pragma unroll
     for (int m = 0; m < 3; m++) {
-      uint32_t k0 = __ldg(csc.ptr[m] + col), k1 = __ldg(csc.ptr[m] + col + 1);
-      if (k0 == k1) continue;
-      fl_t acc = fl_zero();
-      for (uint32_t k = k0; k < k1; k++)
-        acc = fl_add(acc, fl_mul(ldg_fl(e + __ldg(csc.idx[m] + k)), ldg_fl(csc.val[m] + k)));
-      tot = fl_add(tot, fl_mul(m == 0 ? rA : m == 1 ? rB : rC, acc));
+      if (k0[m] == k1[m]) continue;
+      const fl_t acc = seg_sum(csc.idx[m], csc.val[m], csc.lg[m], e, col, k0[m], k1[m]);
+      tot = fl_add(tot, fl_mul_call(m == 0 ? rA : m == 1 ? rB : rC, acc));
     }
     st_fl(out + col, tot);
   }
 }
 cudaError_t k_spmvT3_combine(const Csr& csc, uint32_t num_cols, const fl_t* e, fl_t rA, fl_t rB, fl_t rC, fl_t* out,
                              cudaStream_t s) {
-  spmvT3_kernel<<<grid_for(num_cols, 128), 128, 0, s>>>(csc, num_cols, e, rA, rB, rC, out);
+  cudaError_t err = sp_long_pass(csc, e, s);
+  if (err != cudaSuccess) return err;
+  { KProf kp_("spmvT3_kernel", s); spmvT3_kernel<<<grid_for(num_cols, 128), 128, 0, s>>>(csc, num_cols, e, rA, rB, rC, out); }
   return SB_LAUNCHED();
 }
 
@@ -544,15 +680,15 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   Mailbox mb{w.host_result, w.host_flag, w.seq};
   if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
     unsigned gl = lat_grid(newlen / 2, w);
-    if (do_bind) sc_cubic_lat_kernel<true><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
-    else sc_cubic_lat_kernel<false><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+    if (do_bind) { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<true><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+    else { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<false><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
   const bool compact = g <= kCompactBlocks;
-  if (do_bind && compact) sc_cubic_kernel<true, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
-  else if (do_bind) sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
-  else if (compact) sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
-  else sc_cubic_kernel<false, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb);
+  if (do_bind && compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (do_bind) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   return SB_LAUNCHED();
 }
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s) {
@@ -561,15 +697,15 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
   Mailbox mb{w.host_result, w.host_flag, w.seq};
   if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
     unsigned gl = lat_grid(newlen / 2, w);
-    if (do_bind) sc_quad_lat_kernel<true><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
-    else sc_quad_lat_kernel<false><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+    if (do_bind) { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<true><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+    else { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<false><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
   const bool compact = g <= kCompactBlocks;
-  if (do_bind && compact) sc_quad_kernel<true, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
-  else if (do_bind) sc_quad_kernel<true, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
-  else if (compact) sc_quad_kernel<false, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
-  else sc_quad_kernel<false, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb);
+  if (do_bind && compact) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<true, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (do_bind) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<true, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (compact) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<false, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+  else { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<false, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
   return SB_LAUNCHED();
 }
 
@@ -616,10 +752,10 @@ cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rs
   uint32_t jc = bound_chunks(Lsize, Rsize), jper = (Lsize + jc - 1) / jc;
   jc = (Lsize + jper - 1) / jper;
   dim3 grid((Rsize + 127) / 128, jc);
-  bound_partial_kernel<<<grid, 128, 0, s>>>(Z, Lv, Lsize, Rsize, jper, tmp);
+  { KProf kp_("bound_partial_kernel", s); bound_partial_kernel<<<grid, 128, 0, s>>>(Z, Lv, Lsize, Rsize, jper, tmp); }
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  bound_sum_kernel<<<(Rsize + 127) / 128, 128, 0, s>>>(tmp, Rsize, jc, out);
+  { KProf kp_("bound_sum_kernel", s); bound_sum_kernel<<<(Rsize + 127) / 128, 128, 0, s>>>(tmp, Rsize, jc, out); }
   return SB_LAUNCHED();
 }
 __global__ void dot_small_kernel(const fl_t* __restrict__ a, const fl_t* __restrict__ b, uint32_t n, fl_t* out) {
@@ -631,7 +767,7 @@ __global__ void dot_small_kernel(const fl_t* __restrict__ a, const fl_t* __restr
   if (threadIdx.x == 0) st_fl(out, acc[0]);
 }
 cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cudaStream_t s) {
-  dot_small_kernel<<<1, 1024, 0, s>>>(a, b, n, out);
+  { KProf kp_("dot_small_kernel", s); dot_small_kernel<<<1, 1024, 0, s>>>(a, b, n, out); }
   return SB_LAUNCHED();
 }
 
@@ -651,7 +787,7 @@ __global__ void __launch_bounds__(256) dot3_kernel(const fl_t* __restrict__ e, c
   grid_sum_fl<3>(acc, smem, partials, counter, result);
 }
 cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC, size_t n, const ScWork& w, cudaStream_t s) {
-  dot3_kernel<<<sc_grid(n, w), 256, 0, s>>>(e, yA, yB, yC, n, w.partials, w.counter, w.result);
+  { KProf kp_("dot3_kernel", s); dot3_kernel<<<sc_grid(n, w), 256, 0, s>>>(e, yA, yB, yC, n, w.partials, w.counter, w.result); }
   return SB_LAUNCHED();
 }
 
@@ -737,8 +873,8 @@ cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t*
                           uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL,
                           fl_t* sR, cudaStream_t s) {
   const unsigned row_blocks = (Rsize + kBulletThreads - 1) / kBulletThreads;
-  bullet_step_kernel<<<row_blocks + 1, kBulletThreads, 0, s>>>(a_in, b_in, a_out, b_out, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv,
-                                                              blind_L, blind_R, sL, sR);
+  { KProf kp_("bullet_step_kernel", s); bullet_step_kernel<<<row_blocks + 1, kBulletThreads, 0, s>>>(a_in, b_in, a_out, b_out, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv,
+                                                              blind_L, blind_R, sL, sR); }
   return SB_LAUNCHED();
 }
 __global__ void scale_from_mont_kernel(const fl_t* __restrict__ coeff, fl_t d, uint32_t n, fl_t* __restrict__ out) {
@@ -746,7 +882,7 @@ __global__ void scale_from_mont_kernel(const fl_t* __restrict__ coeff, fl_t d, u
     st_fl(out + i, fl_from_mont(fl_mul(ld_fl(coeff + i), d)));
 }
 cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s) {
-  scale_from_mont_kernel<<<grid_for(n, 128), 128, 0, s>>>(coeff, d, n, out);
+  { KProf kp_("scale_from_mont_kernel", s); scale_from_mont_kernel<<<grid_for(n, 128), 128, 0, s>>>(coeff, d, n, out); }
   return SB_LAUNCHED();
 }
 
@@ -829,19 +965,19 @@ cudaError_t k_snark_dense(const Csr& csr, const uint32_t* const op_csr[3], uint3
   r.N = c.N = N;
   // comb_ops = row addr | row read_ts | col addr | col read_ts | val | zero padding   (5 x 3 blocks of N, then N zeros)
   dim3 grid(grid_for(N, 256), 3);
-  snark_ops_kernel<<<grid, 256, 0, s>>>(r, comb_ops, comb_ops + (size_t)3 * N, comb_ops + (size_t)12 * N);
+  { KProf kp_("snark_ops_kernel", s); snark_ops_kernel<<<grid, 256, 0, s>>>(r, comb_ops, comb_ops + (size_t)3 * N, comb_ops + (size_t)12 * N); }
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  snark_ops_kernel<<<grid, 256, 0, s>>>(c, comb_ops + (size_t)6 * N, comb_ops + (size_t)9 * N, nullptr);
+  { KProf kp_("snark_ops_kernel", s); snark_ops_kernel<<<grid, 256, 0, s>>>(c, comb_ops + (size_t)6 * N, comb_ops + (size_t)9 * N, nullptr); }
   e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  fl_fill_zero_kernel<<<grid_for(N, 256), 256, 0, s>>>(comb_ops + (size_t)15 * N, N);
+  { KProf kp_("fl_fill_zero_kernel", s); fl_fill_zero_kernel<<<grid_for(N, 256), 256, 0, s>>>(comb_ops + (size_t)15 * N, N); }
   e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(r, cells, comb_mem);
+  { KProf kp_("snark_audit_kernel", s); snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(r, cells, comb_mem); }
   e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
-  snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(c, cells, comb_mem + cells);
+  { KProf kp_("snark_audit_kernel", s); snark_audit_kernel<<<grid_for(cells, 256), 256, 0, s>>>(c, cells, comb_mem + cells); }
   return SB_LAUNCHED();
 }
 
@@ -864,7 +1000,7 @@ __global__ void snark_deref_kernel(const fl_t* __restrict__ comb_ops, const fl_t
   }
 }
 cudaError_t k_snark_deref(const fl_t* comb_ops, const fl_t* mem_rx, const fl_t* mem_ry, uint32_t N, fl_t* out, cudaStream_t s) {
-  snark_deref_kernel<<<grid_for((size_t)8 * N, 256), 256, 0, s>>>(comb_ops, mem_rx, mem_ry, N, out);
+  { KProf kp_("snark_deref_kernel", s); snark_deref_kernel<<<grid_for((size_t)8 * N, 256), 256, 0, s>>>(comb_ops, mem_rx, mem_ry, N, out); }
   return SB_LAUNCHED();
 }
 
@@ -933,13 +1069,13 @@ __global__ void __launch_bounds__(512) prod_tail_kernel(ProdTrees t, uint32_t ta
 // one side: trees[0] = init, [1..3] = read, [4..6] = write, [7] = audit (buffers of 2 len scalars, layer 0 written here)
 cudaError_t k_snark_hash_layer(const fl_t* mem, const fl_t* addr, const fl_t* ts, const fl_t* audit_ts, uint32_t N, uint32_t cells,
                                fl_t r_hash, fl_t r_hash_sqr, fl_t r_ms, fl_t* const trees[8], cudaStream_t s) {
-  snark_hash_mem_kernel<<<grid_for(cells, 256), 256, 0, s>>>(mem, audit_ts, cells, r_hash, r_hash_sqr, r_ms, trees[0], trees[7]);
+  { KProf kp_("snark_hash_mem_kernel", s); snark_hash_mem_kernel<<<grid_for(cells, 256), 256, 0, s>>>(mem, audit_ts, cells, r_hash, r_hash_sqr, r_ms, trees[0], trees[7]); }
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
   HashOpsOut o;
   for (int m = 0; m < 3; m++) { o.read[m] = trees[1 + m]; o.write[m] = trees[4 + m]; }
   dim3 grid(grid_for(N, 256), 3);
-  snark_hash_ops_kernel<<<grid, 256, 0, s>>>(mem, addr, ts, N, r_hash, r_hash_sqr, r_ms, o);
+  { KProf kp_("snark_hash_ops_kernel", s); snark_hash_ops_kernel<<<grid, 256, 0, s>>>(mem, addr, ts, N, r_hash, r_hash_sqr, r_ms, o); }
   return SB_LAUNCHED();
 }
 // ntrees <= 16 product circuits at once; products[ntrees] canonical
@@ -955,11 +1091,11 @@ cudaError_t k_prod_trees(fl_t* const bufs[], const uint32_t lens[], int ntrees, 
   const uint32_t tail = 1024;
   for (uint32_t k = 0; (maxlen >> k) > tail; k++) {
     dim3 grid(grid_for((maxlen >> k) / 2, 256, 4), ntrees);
-    prod_layer_kernel<<<grid, 256, 0, s>>>(t, k, tail);
+    { KProf kp_("prod_layer_kernel", s); prod_layer_kernel<<<grid, 256, 0, s>>>(t, k, tail); }
     cudaError_t e = SB_LAUNCHED();
     if (e != cudaSuccess) return e;
   }
-  prod_tail_kernel<<<ntrees, 512, 0, s>>>(t, tail, products);
+  { KProf kp_("prod_tail_kernel", s); prod_tail_kernel<<<ntrees, 512, 0, s>>>(t, tail, products); }
   return SB_LAUNCHED();
 }
 
@@ -1189,13 +1325,13 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   MsmPlan p = msm_plan(rows, n);
   dim3 grid(p.splits, rows);
   if (ev) cudaEventRecord(ev[0], s);
-  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index, p.tpt,
-                                             reinterpret_cast<ge_t*>(scratch));
+  { KProf kp_("msm_fixed_kernel", s); msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, extra_h, h_index, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch)); }
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
-  msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
-      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, nullptr, 0);
+  { KProf kp_("msm_finish_kernel", s); msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
+      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, nullptr, 0); }
   return SB_LAUNCHED();
 }
 // The same in two halves: the row sums first (no blinds needed), then blind*h + compression.
@@ -1205,8 +1341,8 @@ cudaError_t msm_fixed_rows(const MsmTable& t, const fl_t* scalars, size_t stride
   MsmPlan p = msm_plan(rows, n);
   dim3 grid(p.splits, rows);
   if (ev) cudaEventRecord(ev[0], s);
-  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, nullptr, 0, p.tpt,
-                                             reinterpret_cast<ge_t*>(scratch));
+  { KProf kp_("msm_fixed_kernel", s); msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, nullptr, 0, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch)); }
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   return e;
@@ -1218,16 +1354,16 @@ cudaError_t msm_fixed_rows_part(const MsmTable& t, const fl_t* scalars, size_t s
   if (!nrows) return cudaSuccess;
   MsmPlan p = msm_plan(total_rows, n);
   dim3 grid(p.splits, nrows);
-  msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars + (size_t)row0 * stride, stride, n, nullptr, 0, p.tpt,
-                                             reinterpret_cast<ge_t*>(scratch) + (size_t)row0 * p.splits);
+  { KProf kp_("msm_fixed_kernel", s); msm_fixed_kernel<<<grid, p.block, 0, s>>>(t.tbl, t.c, t.windows, scalars + (size_t)row0 * stride, stride, n, nullptr, 0, p.tpt,
+                                             reinterpret_cast<ge_t*>(scratch) + (size_t)row0 * p.splits); }
   return SB_LAUNCHED();
 }
 cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const fl_t* extra_h, uint32_t h_index, const void* scratch,
                              uint8_t* out32, cudaStream_t s) {
   if (!rows) return cudaSuccess;
   MsmPlan p = msm_plan(rows, n);
-  msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
-      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, extra_h, h_index);
+  { KProf kp_("msm_finish_kernel", s); msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
+      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, extra_h, h_index); }
   return SB_LAUNCHED();
 }
 
@@ -1338,8 +1474,8 @@ cudaError_t msm_small(const MsmTable& t, const fl_t* scalars, size_t stride, uin
                       unsigned int* counters, void* out_ext, uint32_t* host_flag, uint32_t seq, cudaStream_t s) {
   if (!rows) return cudaSuccess;
   dim3 grid(msm_small_blocks(rows, n, t.windows), rows);
-  msm_small_kernel<<<grid, 256, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, reinterpret_cast<ge_t*>(scratch), counters,
-                                        reinterpret_cast<ge_t*>(out_ext), host_flag, seq);
+  { KProf kp_("msm_small_kernel", s); msm_small_kernel<<<grid, 256, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, reinterpret_cast<ge_t*>(scratch), counters,
+                                        reinterpret_cast<ge_t*>(out_ext), host_flag, seq); }
   return SB_LAUNCHED();
 }
 // up to four scalars (the first element of each source) to a host mailbox, then the flag
@@ -1354,7 +1490,7 @@ __global__ void mail_kernel(const fl_t* p0, const fl_t* p1, const fl_t* p2, cons
 }
 cudaError_t k_mail(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int n, fl_t* host, uint32_t* host_flag,
                    uint32_t seq, cudaStream_t s) {
-  mail_kernel<<<1, 32, 0, s>>>(p0, p1, p2, p3, n, host, host_flag, seq);
+  { KProf kp_("mail_kernel", s); mail_kernel<<<1, 32, 0, s>>>(p0, p1, p2, p3, n, host, host_flag, seq); }
   return SB_LAUNCHED();
 }
 // the first `count` entries of up to four tables to a host mailbox (table k at host + k*count), then the flag
@@ -1371,14 +1507,33 @@ __global__ void mail_tables_kernel(const fl_t* p0, const fl_t* p1, const fl_t* p
 }
 cudaError_t k_mail_tables(const fl_t* p0, const fl_t* p1, const fl_t* p2, const fl_t* p3, int ntab, uint32_t count, fl_t* host,
                           uint32_t* host_flag, uint32_t seq, cudaStream_t s) {
-  mail_tables_kernel<<<1, 256, 0, s>>>(p0, p1, p2, p3, ntab, count, host, host_flag, seq);
+  { KProf kp_("mail_tables_kernel", s); mail_tables_kernel<<<1, 256, 0, s>>>(p0, p1, p2, p3, ntab, count, host, host_flag, seq); }
   return SB_LAUNCHED();
 }
 
 // ------------------------------------------------------------------ table build
-// thread per (base, window, chunk of CH multiples): tbl[base][w][m-1] = m * 2^(c*w) * G_base as affine Niels.
+// tbl[base][w][m-1] = m * 2^(c*w) * G_base as affine Niels, in two kernels:
+//   msm_winbase_kernel  thread per base: B_w = 2^(c*w) * G for every window w (252 doublings once per base, instead of
+//                       c*w doublings in every thread of the second kernel -- that was 40 % of the build);
+//   msm_table_kernel    thread per (base, window, chunk of kTblChunk multiples): m0 * B_w by double-and-add from the
+//                       top set bit of m0, then the run of multiples, one shared inversion per chunk.
 static constexpr int kTblChunk = 64;
-__global__ void __launch_bounds__(64) msm_table_kernel(const fp_t* __restrict__ affine_xy, uint32_t nbases, uint32_t c,
+__global__ void __launch_bounds__(64) msm_winbase_kernel(const fp_t* __restrict__ affine_xy, uint32_t nbases, uint32_t c,
+                                                         uint32_t windows, ge_t* __restrict__ winbase) {
+  const uint32_t base = blockIdx.x * blockDim.x + threadIdx.x;
+  if (base >= nbases) return;
+  ge_t P;
+  P.X = ldg_fp(affine_xy + 2 * (size_t)base);
+  P.Y = ldg_fp(affine_xy + 2 * (size_t)base + 1);
+  P.Z = fp_one();
+  P.T = fp_mul_call(P.X, P.Y);
+  for (uint32_t w = 0; w < windows; w++) {
+    winbase[(size_t)base * windows + w] = P;
+    if (w + 1 < windows)
+      for (uint32_t k = 0; k < c; k++) P = ge_double_call(P);
+  }
+}
+__global__ void __launch_bounds__(64) msm_table_kernel(const ge_t* __restrict__ winbase, uint32_t nbases, uint32_t c,
                                                        uint32_t windows, niels_t* __restrict__ tbl) {
   const uint32_t epw = 1u << (c - 1);
   const uint32_t ch = epw < (uint32_t)kTblChunk ? epw : (uint32_t)kTblChunk;
@@ -1389,16 +1544,11 @@ __global__ void __launch_bounds__(64) msm_table_kernel(const fp_t* __restrict__ 
   uint32_t chunk = (uint32_t)(tid % chunks);
   uint32_t w = (uint32_t)((tid / chunks) % windows);
   uint32_t base = (uint32_t)(tid / ((size_t)chunks * windows));
-  ge_t P;
-  P.X = ldg_fp(affine_xy + 2 * (size_t)base);
-  P.Y = ldg_fp(affine_xy + 2 * (size_t)base + 1);
-  P.Z = fp_one();
-  P.T = fp_mul_call(P.X, P.Y);
-  for (uint32_t k = 0; k < c * w; k++) P = ge_double_call(P);
+  const ge_t P = winbase[(size_t)base * windows + w];
   // M = (chunk*ch + 1) * P
   uint32_t m0 = chunk * ch + 1;
-  ge_t M = ge_identity();
-  for (int bit = 15; bit >= 0; bit--) {
+  ge_t M = P;
+  for (int bit = 30 - __clz(m0); bit >= 0; bit--) {
     M = ge_double_call(M);
     if ((m0 >> bit) & 1u) M = ge_add_call(M, P);
   }
@@ -1411,7 +1561,7 @@ __global__ void __launch_bounds__(64) msm_table_kernel(const fp_t* __restrict__ 
     st_fp(&slot[k].yplusx, M.X);
     st_fp(&slot[k].yminusx, M.Y);
     st_fp(&slot[k].xy2d, M.Z);
-    M = ge_add_call(M, P);
+    if (k + 1 < ch) M = ge_add_call(M, P);
   }
   fp_t inv = fp_invert_t<FpCall>(acc);
   for (int k = (int)ch - 1; k >= 0; k--) {
@@ -1432,17 +1582,25 @@ cudaError_t msm_table_build(MsmTable& t, const uint8_t* affine_xy_host, uint32_t
   cudaError_t e = cudaMalloc(&t.tbl, bytes);
   if (e != cudaSuccess) return e;
   fp_t* d_xy = nullptr;
+  ge_t* d_wb = nullptr;
   e = cudaMalloc(&d_xy, (size_t)nbases * 64);
   if (e != cudaSuccess) return e;
+  e = cudaMalloc(&d_wb, (size_t)nbases * t.windows * sizeof(ge_t));
+  if (e != cudaSuccess) { cudaFree(d_xy); return e; }
   e = cudaMemcpyAsync(d_xy, affine_xy_host, (size_t)nbases * 64, cudaMemcpyHostToDevice, s);
-  if (e != cudaSuccess) return e;
-  uint32_t epw = 1u << (c - 1), ch = epw < (uint32_t)kTblChunk ? epw : (uint32_t)kTblChunk;
-  size_t total = (size_t)nbases * t.windows * (epw / ch);
-  msm_table_kernel<<<(unsigned)((total + 63) / 64), 64, 0, s>>>(d_xy, nbases, c, t.windows, t.tbl);
-  e = SB_LAUNCHED();
-  if (e != cudaSuccess) return e;
-  e = cudaStreamSynchronize(s);
+  if (e == cudaSuccess) {
+    { KProf kp_("msm_winbase_kernel", s); msm_winbase_kernel<<<(nbases + 63) / 64, 64, 0, s>>>(d_xy, nbases, c, t.windows, d_wb); }
+    e = SB_LAUNCHED();
+  }
+  if (e == cudaSuccess) {
+    uint32_t epw = 1u << (c - 1), ch = epw < (uint32_t)kTblChunk ? epw : (uint32_t)kTblChunk;
+    size_t total = (size_t)nbases * t.windows * (epw / ch);
+    { KProf kp_("msm_table_kernel", s); msm_table_kernel<<<(unsigned)((total + 63) / 64), 64, 0, s>>>(d_wb, nbases, c, t.windows, t.tbl); }
+    e = SB_LAUNCHED();
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   cudaFree(d_xy);
+  cudaFree(d_wb);
   return e;
 }
 void msm_table_free(MsmTable& t) {

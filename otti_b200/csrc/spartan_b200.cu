@@ -13,6 +13,7 @@
 #include <cstring>
 #include <mutex>
 #include <random>
+#include <thread>
 
 #include "../../include/spartan_b200.h"
 #include "../../include/spartan_b200_kernels.h"
@@ -110,6 +111,28 @@ static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint6
         DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
         SB_CUDA(od.alloc(nnz ? nnz : 1));
         if (nnz) SB_CUDA(cudaMemcpy(od.p, op.data(), nnz * 4, cudaMemcpyHostToDevice));
+      }
+      {  // long segments -> chunk lists (dev.hpp LongSegs)
+        std::vector<uint32_t> lseg, lfirst, lo, hi, big;
+        for (uint64_t sgm = 0; sgm < nseg; sgm++) {
+          const uint32_t a = ptr[sgm], b = ptr[sgm + 1];
+          if (b - a <= sb::kLongSeg) continue;
+          lseg.push_back((uint32_t)sgm);
+          lfirst.push_back((uint32_t)lo.size());
+          for (uint32_t q = a; q < b; q += sb::kSegChunk) { lo.push_back(q); hi.push_back(std::min(b, q + sb::kSegChunk)); }
+          if (lo.size() - lfirst.back() > sb::kSumInline) big.push_back((uint32_t)lseg.size() - 1);
+        }
+        lfirst.push_back((uint32_t)lo.size());
+        sd.nlong[m] = (uint32_t)lseg.size(); sd.nchunks[m] = (uint32_t)lo.size(); sd.nbig[m] = (uint32_t)big.size();
+        auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
+          cudaError_t e = d.alloc(v.size() ? v.size() : 1);
+          if (e != cudaSuccess || v.empty()) return e;
+          return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
+        };
+        SB_CUDA(put(sd.lg_seg[m], lseg)); SB_CUDA(put(sd.lg_first[m], lfirst)); SB_CUDA(put(sd.lg_lo[m], lo));
+        SB_CUDA(put(sd.lg_hi[m], hi)); SB_CUDA(put(sd.lg_big[m], big));
+        SB_CUDA(sd.lg_partial[m].alloc(lo.size() ? lo.size() : 1));
+        SB_CUDA(sd.lg_reduced[m].alloc(lseg.size() ? lseg.size() : 1));
       }
       SB_CUDA(sd.ptr[m].alloc(nseg + 1));
       SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
@@ -347,6 +370,7 @@ int sb200_instance_is_sat(const sb200_instance* h, const uint8_t* vars32, uint64
                           uint64_t n_inputs, int* sat_out) {
   if (!h || !sat_out) return SB200_ERR_ARG;
   const Instance& inst = *reinterpret_cast<const Instance*>(h);
+  std::lock_guard<std::mutex> inst_lock(inst.mu);  // the handle's workspace, stream and scratch serve one call at a time
   if (n_vars > inst.num_vars) { set_error("InvalidNumberOfInputs"); return SB200_ERR_INVALID_NUMBER_OF_INPUTS; }      // lib.rs:233-235
   if (n_inputs != inst.num_inputs) { set_error("InvalidNumberOfInputs"); return SB200_ERR_INVALID_NUMBER_OF_INPUTS; }  // lib.rs:237-239
   if (inst.world > 1) { set_error("is_sat needs an unsharded instance"); return SB200_ERR_ARG; }
@@ -383,6 +407,12 @@ void sb200_instance_free(sb200_instance* h) { delete reinterpret_cast<Instance*>
 // ------------------------------------------------------------------------------ generators
 int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs,
                    sb200_gens** out) {
+  uint64_t expected = 0;  // 0 = many proofs: the widest tables that fit
+  if (const char* env = getenv("SB200_PROOFS_EXPECTED")) expected = strtoull(env, nullptr, 10);
+  return sb200_gens_new_for(label, label_len, num_cons, num_vars, num_inputs, expected, out);
+}
+int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs,
+                       uint64_t proofs_expected, sb200_gens** out) {
   (void)num_cons;
   if (!out) return SB200_ERR_ARG;
   *out = nullptr;
@@ -409,21 +439,27 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
     Shake256Xof xof;
     xof.update(label, label_len);
     xof.update(kBase, 32);  // GROUP_BASEPOINT_COMPRESSED, group.rs:23-24
-    for (size_t i = 0; i < npts; i++) {
-      uint8_t ub[64];
-      xof.read(ub, 64);
-      pts[i] = ge_from_uniform_bytes(ub);
-    }
+    std::vector<uint8_t> stream(64 * npts);
+    xof.read(stream.data(), stream.size());
+    // from_uniform_bytes is two Elligator maps (~15 us a point): spread over the host cores
+    unsigned nthr = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+    if (g_bound_cpus > 0) nthr = std::min<unsigned>(nthr, (unsigned)g_bound_cpus);
+    if (npts < 64) nthr = 1;
+    auto work = [&](unsigned t) { for (size_t i = t; i < npts; i += nthr) pts[i] = ge_from_uniform_bytes(&stream[64 * i]); };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nthr; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
   }
   g->G.assign(pts.begin(), pts.begin() + R);
   g->Q = pts[R];
   g->h = pts[R + 1];
   for (int i = 0; i < 4; i++) g->G4[i] = pts[i];
   g->h4 = pts[4];
-  for (int i = 0; i < 4; i++) g->fb_G4[i].build(g->G4[i]);
-  g->fb_h4.build(g->h4);
-  g->fb_Q.build(g->Q);
-  g->fb_h.build(g->h);
+  for (int i = 0; i < 4; i++) g->fb_G4[i].point = g->G4[i];
+  g->fb_h4.point = g->h4;
+  g->fb_Q.point = g->Q;
+  g->fb_h.point = g->h;
   // device tables over [G..., h, Q]: affine coordinates with one shared inversion
   std::vector<Ge> bases(g->G);
   bases.push_back(g->h);
@@ -458,9 +494,18 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
       long v = atol(env);
       if (v > 0) budget = (size_t)v << 20;
     }
-    for (uint32_t cc = 9; cc <= 16; cc++) {
-      size_t bytes = bases.size() * (size_t)(252 / cc + 1) * ((size_t)1 << (cc - 1)) * 96;
-      if (bytes <= budget) c = cc;
+    // proofs_expected > 0: the width that minimises  table build + proofs_expected x commitment,  in mixed additions:
+    // an entry of the table costs ~3 (a full addition + its share of the chunk's inversion and normalisation), a
+    // term of the witness one per window.  A one-shot caller (spzk: gens + one proof per process, main.rs:71-85) gets
+    // a table that is built in milliseconds instead of the widest one that fits the HBM.
+    double best = 0;
+    for (uint32_t cc = 8; cc <= 16; cc++) {
+      const size_t W = 252 / cc + 1, entries = bases.size() * W * ((size_t)1 << (cc - 1));
+      if (entries * 96 > budget && cc > 8) continue;
+      if (proofs_expected == 0) { c = cc; continue; }
+      const double terms = (double)nvp + (double)((size_t)1 << (ell / 2));
+      const double cost = 3.0 * (double)entries + (double)proofs_expected * terms * (double)W;
+      if (best == 0 || cost < best) { best = cost; c = cc; }
     }
   }
   if (const char* env = getenv("SB200_MSM_WINDOW")) {
@@ -478,10 +523,40 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
   // [G_0..G_{R-1}, h, Q].  SB200_HOST_WIDE=0 keeps the narrow host tables.
   {
     const char* hw = getenv("SB200_HOST_WIDE");
-    if (c >= 10 && !(hw && atoi(hw) == 0)) {
+    const bool want_wide = !(hw && atoi(hw) == 0);
+    FixedBase* fbs[7] = {&g->fb_G4[0], &g->fb_G4[1], &g->fb_G4[2], &g->fb_G4[3], &g->fb_h4, &g->fb_Q, &g->fb_h};
+    const size_t point_of[7] = {0, 1, 2, 3, 4, (size_t)R, (size_t)R + 1};
+    if (want_wide && c < 13) {
+      // narrow device windows (one-shot generators): the seven tail generators get a table of their own, 12- or 13-bit
+      // windows (30 / 55 MB), built by the same kernels and copied to the host as a whole
+      const uint32_t ch = proofs_expected > 0 && proofs_expected <= 4 ? 12 : 13;
+      std::vector<uint8_t> xy7(7 * 64);
+      for (int k = 0; k < 7; k++) {
+        const size_t pi = point_of[k];
+        const size_t bi = pi < R ? pi : (pi == R ? (size_t)R + 1 : (size_t)R);  // position among [G..., h, Q]
+        if (pi <= (size_t)R + 1) memcpy(&xy7[64 * k], &xy[64 * bi], 64);
+        else {  // R < 5: a stream point beyond the bases (gens_3 / gens_4 of a tiny instance)
+          Fe zi = fe_invert(pts[pi].Z);
+          fe_tobytes(fe_mul(pts[pi].X, zi), &xy7[64 * k]);
+          fe_tobytes(fe_mul(pts[pi].Y, zi), &xy7[64 * k + 32]);
+        }
+      }
+      sb::MsmTable t7;
+      cudaError_t e7 = sb::msm_table_build(t7, xy7.data(), 7, ch, 0);
+      const size_t bytes = t7.entries_per_base() * (size_t)96;
+      if (e7 == cudaSuccess) {
+        g->wide_store[0].resize(7 * bytes);
+        e7 = cudaMemcpy(g->wide_store[0].data(), t7.tbl, 7 * bytes, cudaMemcpyDeviceToHost);
+      }
+      sb::msm_table_free(t7);
+      if (e7 != cudaSuccess) {
+        set_error(std::string("host tables of the tail generators: ") + cudaGetErrorString(e7));
+        delete g;
+        return SB200_ERR_CUDA;
+      }
+      for (int k = 0; k < 7; k++) fbs[k]->set_wide(g->wide_store[0].data() + (size_t)k * bytes, ch, 252u / ch + 1u);
+    } else if (want_wide) {
       const size_t bytes = g->table.entries_per_base() * (size_t)96;  // sizeof(niels_t)
-      FixedBase* fbs[7] = {&g->fb_G4[0], &g->fb_G4[1], &g->fb_G4[2], &g->fb_G4[3], &g->fb_h4, &g->fb_Q, &g->fb_h};
-      const size_t point_of[7] = {0, 1, 2, 3, 4, (size_t)R, (size_t)R + 1};
       SB_CUDA(cudaDeviceSynchronize());
       for (int k = 0; k < 7; k++) {
         const size_t pi = point_of[k];
@@ -498,6 +573,8 @@ int sb200_gens_new(const uint8_t* label, size_t label_len, uint64_t num_cons, ui
         fbs[k]->set_wide(g->wide_store[k].data(), g->table.c, g->table.windows);
       }
     }
+    for (int k = 0; k < 7; k++)
+      if (fbs[k]->wide == nullptr) fbs[k]->build(fbs[k]->point);  // cache-resident 8-bit tables (SB200_HOST_WIDE=0, or a missing slice)
   }
   *out = reinterpret_cast<sb200_gens*>(g);
   return SB200_OK;
@@ -594,6 +671,7 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
   int rc = ensure_device();
   if (rc) return rc;
   const Instance& inst = *reinterpret_cast<const Instance*>(hi);
+  std::lock_guard<std::mutex> inst_lock(inst.mu);  // the handle's workspace, stream and scratch serve one call at a time
   const Gens& gens = *reinterpret_cast<const Gens*>(hg);
   uint8_t seed[64];
   if (tape_seed64) memcpy(seed, tape_seed64, 64);
@@ -633,6 +711,7 @@ int sb200_witness_upload(const sb200_instance* hi, const sb200_gens* hg, const u
   int rc = ensure_device();
   if (rc) return rc;
   const Instance& inst = *reinterpret_cast<const Instance*>(hi);
+  std::lock_guard<std::mutex> inst_lock(inst.mu);  // the handle's workspace, stream and scratch serve one call at a time
   if (n_vars > inst.num_vars) return SB200_ERR_ARG;
   rc = workspace_init(inst, *reinterpret_cast<const Gens*>(hg));
   if (rc) return rc;

@@ -39,6 +39,18 @@ class R1cs:
         return R1cs(h)
 
     @staticmethod
+    def from_pointers(circuit, header, witness):
+        """the same from three (pointer, length) pairs: no copy of a multi-hundred-megabyte circuit file"""
+        L = lib()
+        h = C.c_void_p()
+        rc = L.sb200_zkif_parse(circuit[0], C.c_size_t(circuit[1]), header[0], C.c_size_t(header[1]), witness[0],
+                                C.c_size_t(witness[1]), C.byref(h))
+        if rc == -104:
+            raise ZkifError((L.sb200_last_error() or b"").decode())
+        _check(rc)
+        return R1cs(h)
+
+    @staticmethod
     def from_files(circuit_fn, inputs_fn, witness_fn):
         """Argument order of `spzk prove --nizk <circuit.zkif> <inputs.zkif> <witness.zkif>` (main.rs:18)."""
         with open(circuit_fn, "rb") as f:
@@ -48,6 +60,13 @@ class R1cs:
         with open(witness_fn, "rb") as f:
             w = f.read()
         return R1cs.from_buffers(c, i, w)
+
+    def matrix_arrays(self, m):
+        """(rows, cols, vals) of matrix m as bytes (u64 LE, u64 LE, 32 bytes each)"""
+        rows, cols, vals = C.POINTER(C.c_uint64)(), C.POINTER(C.c_uint64)(), C.POINTER(C.c_uint8)()
+        _check(lib().sb200_r1cs_matrix(self.h, C.c_int(m), C.byref(rows), C.byref(cols), C.byref(vals)))
+        n = self.nnz[m]
+        return (C.string_at(rows, 8 * n), C.string_at(cols, 8 * n), C.string_at(vals, 32 * n)) if n else (b"", b"", b"")
 
     def matrix(self, m):
         """COO triples of A (m=0), B (1) or C (2): [(row, col, 32 bytes)] in the reference's order."""
@@ -75,8 +94,10 @@ class R1cs:
         _check(lib().sb200_r1cs_instance(self.h, C.c_int(rank), C.c_int(world), C.byref(h)))
         return Instance(h)
 
-    def nizk_public_params(self):
-        return NIZKGens.new(self.num_cons, self.num_vars, self.num_inputs)
+    def nizk_public_params(self, proofs_expected=None):
+        """`R1cs::nizk_public_params` (lib.rs:146-152).  spzk makes one proof per process and times the generators
+        with it (main.rs:71-85): pass proofs_expected=1 for tables sized for that."""
+        return NIZKGens.new(self.num_cons, self.num_vars, self.num_inputs, proofs_expected)
 
     def __del__(self):
         if getattr(self, "h", None):

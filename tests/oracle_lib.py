@@ -262,6 +262,20 @@ class Instance:
         return Instance(h)
 
     @staticmethod
+    def new_arrays(num_cons, num_vars, num_inputs, mats):
+        """mats: three (rows u64 ctypes array, cols u64 ctypes array, vals u8 ctypes array, nnz)"""
+        rows = (C.c_void_p * 3)(*[C.cast(m[0], C.c_void_p) for m in mats])
+        cols = (C.c_void_p * 3)(*[C.cast(m[1], C.c_void_p) for m in mats])
+        vals = (C.c_void_p * 3)(*[C.cast(m[2], C.c_void_p) for m in mats])
+        nnz = (C.c_uint64 * 3)(*[m[3] for m in mats])
+        err = C.c_int(0)
+        h = lib().orc_instance_new(C.c_size_t(num_cons), C.c_size_t(num_vars), C.c_size_t(num_inputs), rows, cols, vals, nnz,
+                                   C.byref(err))
+        if not h:
+            raise ValueError({-5: "InvalidScalar", -6: "InvalidIndex"}.get(err.value, str(err.value)))
+        return Instance(h)
+
+    @staticmethod
     def synthetic(num_cons, num_vars, num_inputs, seed):
         v = _out(32 * num_vars)
         i = _out(32 * num_inputs)

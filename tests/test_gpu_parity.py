@@ -145,6 +145,96 @@ def test_multiply_vec_and_eval_table(sb, dims):
     assert bytes(got) == want
 
 
+def test_sparse_kernels_long_segments(sb):
+    """Rows / columns longer than one thread's share (dev.hpp kLongSeg = 16, kSegChunk = 512, kSumInline = 8): segments of
+    exactly 16, 17, 512, 513, 4096, 4097 and 9000 entries, as rows AND as columns, coefficients +1 / -1 / general
+    (the +-1 fast path), duplicates included.  Same bytes as the oracle's insertion-order loops."""
+    rng = random.Random(99)
+    nc, nv, ni = 9500, 9400, 6
+    ncols = nv + 1 + ni
+    lens = [16, 17, 512, 513, 4096, 4097, 9000]
+    val = lambda: rng.choice([1, 1, ELL - 1, 2, rng.randrange(ELL), rng.randrange(2**32)]).to_bytes(32, "little")
+    mats = []
+    for m in range(3):
+        M = []
+        for k, ln in enumerate(lens):
+            row = 3 * k + m  # a long row: ln entries in distinct columns (plus one duplicate)
+            cols = rng.sample(range(ncols), min(ln, ncols))
+            M += [(row, c, val()) for c in cols] + [(row, cols[0], val())]
+            col = 40 + 5 * k + m  # a long column: ln entries in distinct rows
+            rows = rng.sample(range(nc), min(ln, nc))
+            M += [(r, col if col != nv else col + 1, val()) for r in rows]
+        M += [(rng.randrange(nc), nv, val()) for _ in range(7000)]  # the constant column on top
+        M += [(rng.randrange(nc), rng.randrange(ncols), val()) for _ in range(5000)]
+        rng.shuffle(M)
+        mats.append(M)
+    A, B, Cm = mats
+    oi = O.Instance.new(nc, nv, ni, A, B, Cm)
+    pi = sb.Instance.new(nc, nv, ni, A, B, Cm)
+    z = mont(rand_scalars(2 * oi.num_vars, 5))
+    oa, ob, oc = oi.multiply_vec(z)
+    ga, gb, gc = _out(len(oa)), _out(len(oa)), _out(len(oa))
+    assert sb.lib().sb200_k_multiply_vec(pi.h, _buf(z), ga, gb, gc) == 0
+    assert (bytes(ga), bytes(gb), bytes(gc)) == (oa, ob, oc)
+    e = mont(rand_scalars(oi.num_cons, 6))
+    rabc = mont(rand_scalars(3, 7))
+    want = oi.eval_table_abc(e, rabc)
+    got = _out(len(want))
+    assert sb.lib().sb200_k_eval_table_abc(pi.h, _buf(e), _buf(rabc), got) == 0
+    assert bytes(got) == want
+
+
+@pytest.mark.parametrize("c", [2, 5, 8, 11, 13, 16])
+def test_window_sweep_short_scalars(sb, c):
+    """The commitment kernel stops a short scalar after (bitlen-1)/c + 2 windows (kernels.cu msm_fixed_kernel): for every
+    window width, scalars 2^k - 1, 2^k, 2^k + 1 around the multiples of c (where the recoding carry crosses a window
+    boundary), all-ones words, bits and full-size scalars give the oracle's commitment rows."""
+    nv = 256
+    og = O.Gens(nv, nv, 1)
+    os.environ["SB200_MSM_WINDOW"] = str(c)
+    try:
+        pg = sb.NIZKGens.new(nv, nv, 1)
+    finally:
+        os.environ.pop("SB200_MSM_WINDOW", None)
+    assert pg.window_bits == c
+    vals = [0, 1, 2**32 - 1, 2**64 - 1, ELL - 1, 2**252, 2**252 - 1]
+    for m in range(1, 253 // c + 1):
+        k = m * c
+        for kk in (k - 1, k, k + 1):
+            if 0 < kk < 252:
+                vals += [2**kk - 1, 2**kk, 2**kk + 1, 2**kk - 2**(kk - 1) if kk > 1 else 1]
+    vals += [2**(c - 1), 2**(c - 1) + 1, 2**(c - 1) - 1, (2**c - 1) * (2**c + 1)]
+    rng = random.Random(c)
+    while len(vals) % 16:
+        vals.append(rng.randrange(2))
+    vals = vals[:(len(vals) // 16) * 16]
+    L = len(vals) // 16
+    blinds = rand_scalars(L, 50 + c)
+    o = _out(32 * L)
+    assert sb.lib().sb200_k_commit_rows(pg.h, _buf(canon(vals)), C.c_size_t(len(vals)), _buf(canon(blinds)), C.c_size_t(L), o) == 0
+    want = b"".join(og.commit_rows(mont(vals[16 * i:16 * i + 16]), mont([blinds[i]])) for i in range(L))
+    assert bytes(o) == want
+
+
+@pytest.mark.parametrize("s,expected", [(10, 1), (16, 1), (16, 50), (18, 1)])
+def test_one_shot_generators_same_proof(sb, s, expected):
+    """sb200_gens_new_for: the hint changes the window width of the tables (and where the host tables of the tail
+    generators come from), never a proof byte."""
+    n = 1 << s
+    pi, pv, pin = sb.Instance.produce_synthetic_r1cs(n, n, 10, 0x0771)
+    g1 = sb.NIZKGens.new(n, n, 10, proofs_expected=expected)
+    g0 = sb.NIZKGens.new(n, n, 10)
+    assert g1.window_bits <= g0.window_bits
+    if expected == 1:
+        assert g1.window_bits < 13
+    oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x0771)
+    want = O.nizk_prove(oi, ov, oin, O.Gens(n, n, 10), LABEL, TAPE_SEED, 8)
+    for g in (g1, g0):
+        proof = sb.NIZK.prove(pi, pv, pin, g, sb.Transcript.new(LABEL), TAPE_SEED)
+        assert proof.to_bytes() == want
+        assert proof.verify(pi, pin, sb.Transcript.new(LABEL), g) is None
+
+
 @pytest.mark.parametrize("ntab", [4, 2])
 @pytest.mark.parametrize("logn", [1, 2, 5, 9, 12, 15])
 def test_sumcheck_rounds(sb, ntab, logn):
@@ -473,6 +563,14 @@ def test_full_size_properties(sb, s):
     if s == 20:
         assert want_len == 47024  # Spartan/README.md:376, the only byte-level figure the reference publishes
     assert proof.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    # the oracle sees the full-size proof: its own verifier accepts the GPU's bytes, and its own prover (all host
+    # threads; ~4 s at 2^20, ~15-25 s at 2^22) produces the same bytes
+    oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x51 + s)
+    assert ov == bytes(pv.data) and oin == bytes(pin.data)
+    og = O.Gens(n, n, 10)
+    assert O.nizk_verify(oi, oin, og, LABEL, b) == 0
+    assert O.nizk_prove(oi, ov, oin, og, LABEL, TAPE_SEED, os.cpu_count() or 8) == b
+    del oi, og
     os.environ["SB200_H2D_PIECES"] = "1"
     try:
         assert sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), TAPE_SEED).to_bytes() == b
@@ -481,6 +579,9 @@ def test_full_size_properties(sb, s):
     other = sb.NIZK.prove(pi, pv, pin, pg, sb.Transcript.new(LABEL), bytes(64))
     assert other.to_bytes() != b and len(other.to_bytes()) == len(b)
     assert other.verify(pi, pin, sb.Transcript.new(LABEL), pg) is None
+    oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x51 + s)
+    assert O.nizk_verify(oi, oin, O.Gens(n, n, 10), LABEL, other.to_bytes()) == 0
+    del oi
     rng = random.Random(s)
     for off in (40, len(b) // 3, len(b) - 5):
         bad = bytearray(b)

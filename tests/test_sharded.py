@@ -134,7 +134,7 @@ def test_host_tail_rounds_do_not_change_the_proof(world, tail, s, tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,case", [(2, "syn:16"), (4, "syn:16"), (4, "rag:48,40000,3"), (8, "rag:48,33000,3")])
+@pytest.mark.parametrize("world,case", [(2, "syn:16"), (4, "syn:16"), (4, "rag:48,40000,3"), (8, "rag:48,33000,3"), (2, "syn:18"), (4, "syn:18")])
 def test_sharded_witness_exchange(world, case, tmp_path):
     """Witnesses of >= 1 MiB: each rank uploads only its block of commitment rows and reads the other blocks from the
     peers' HBM (CUDA IPC, prover.inc p2p_setup) -- also when the zero padding of a non-power-of-two witness leaves some

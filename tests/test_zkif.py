@@ -146,3 +146,50 @@ def test_prove_otti_shaped_through_zkif(dims):
     proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE_SEED)
     assert proof.to_bytes() == want
     proof.verify(inst, inputs, sb.Transcript.new(LABEL), gens)
+
+
+def test_generated_heavy_constant_column_files():
+    """tools/zkifgen.cpp (the C++ writer behind the 2^18 / 2^20 Otti-shaped cases): its files parse to its own COO
+    triples under both the Python restatement of the reference reader and the product's reader; ~30 % of all entries
+    sit in the constant column."""
+    import zkifgen
+    from otti_b200 import zkif
+    g = zkifgen.OttiShaped(700, 450, 9, seed=5)
+    assert g.const_entries >= 0.25 * sum(g.nnz)
+    c, h, w = (g.file_bytes(k) for k in range(3))
+    spec = zkif_spec.parse(c, h, w)
+    assert [spec[k] for k in "ABC"] == [g.coo_list(m) for m in range(3)]
+    assert spec["vars"] == g.vars_bytes() and spec["inputs"] == g.inputs_bytes()
+    oi = O.Instance.new_arrays(700, 450, 9, [g.coo_arrays(m) + (g.nnz[m],) for m in range(3)])
+    assert oi.is_sat(g.vars_bytes(), g.inputs_bytes()) == 1
+    _same(zkif.R1cs.from_pointers(g.file_ptr(0), g.file_ptr(1), g.file_ptr(2)), spec)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dims", [(1 << 18, 1 << 18, 10), (200000, 1 << 17, 3)])
+def test_prove_otti_shaped_heavy_column_2p18(dims):
+    """An Otti-shaped instance at 2^18 constraints whose constant column holds ~30 % of all non-zero entries (one column of
+    ~2 * 10^5 entries per matrix), through zkinterface: reader == generator's COO, is_sat, proof bytes == oracle,
+    device verify and oracle verify accept."""
+    import otti_b200 as sb
+    import zkifgen
+    from otti_b200 import zkif
+    assert sb.lib().sb200_init(0) == 0
+    nc, nv, ni = dims
+    g = zkifgen.OttiShaped(nc, nv, ni, seed=11)
+    assert g.const_entries >= 0.25 * sum(g.nnz)
+    r = zkif.R1cs.from_pointers(g.file_ptr(0), g.file_ptr(1), g.file_ptr(2))
+    assert (r.num_cons, r.num_vars, r.num_inputs) == dims and r.nnz == g.nnz
+    for m in range(3):
+        rows, cols, vals = g.coo_arrays(m)
+        assert r.matrix_arrays(m) == (bytes(rows)[:8 * g.nnz[m]], bytes(cols)[:8 * g.nnz[m]], bytes(vals)[:32 * g.nnz[m]])
+    inst, vars_, inputs, gens = r.instance(), r.vars_assignment(), r.inputs_assignment(), r.nizk_public_params()
+    assert bytes(vars_.data) == g.vars_bytes()
+    assert inst.is_sat(vars_, inputs)
+    oi = O.Instance.new_arrays(nc, nv, ni, [g.coo_arrays(m) + (g.nnz[m],) for m in range(3)])
+    og = O.Gens(nc, nv, ni)
+    want = O.nizk_prove(oi, g.vars_bytes(), g.inputs_bytes(), og, LABEL, TAPE_SEED, os.cpu_count() or 8)
+    proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE_SEED)
+    assert proof.to_bytes() == want
+    proof.verify(inst, inputs, sb.Transcript.new(LABEL), gens)
+    assert O.nizk_verify(oi, g.inputs_bytes(), og, LABEL, proof.to_bytes()) == 0
