@@ -78,7 +78,7 @@ def test_bench_reference_arm_prints_one_json_line():
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--log-size", "14"],
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = out.stdout.splitlines()
@@ -86,3 +86,4 @@ def test_bench_reference_arm_prints_one_json_line():
     line = json.loads(lines[0])
     assert line["impl"] == "reference" and line["unit"] == "constraints/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+    assert line["config"]["workload"] == "synthetic Spartan R1CS 2^14 constraints = vars, 10 inputs, NIZK::prove"  # == the GPU arm's string
