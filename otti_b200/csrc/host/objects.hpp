@@ -145,7 +145,7 @@ struct Gens {
   Ge h, Q, G4[4], h4;
   // fixed-base tables for the 7 generators of the Fiat-Shamir tail
   FixedBase fb_G4[4], fb_h4, fb_Q, fb_h;
-  std::vector<uint8_t> wide_store[7];  // host copies of the device table slices behind the fb_* above (FixedBase::wide)
+  std::unique_ptr<uint8_t[]> wide_store[7];  // host copies of the device table slices behind the fb_* above (FixedBase::wide)
   sb::MsmTable table;  // device: bases [0,R) = G, R = h, R+1 = Q
   ~Gens() { sb::msm_table_free(table); }
 };

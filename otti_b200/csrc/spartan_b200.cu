@@ -418,6 +418,14 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
   *out = nullptr;
   int rc = ensure_device();
   if (rc) return rc;
+  const bool gtrace = getenv("SB200_TRACE_GENS") != nullptr;  // stage times of this call on stderr
+  double gt0 = now_s();
+  auto gmark = [&](const char* what) {
+    if (!gtrace) return;
+    double t = now_s();
+    fprintf(stderr, "[sb200-gens] %8.3f ms  %s\n", (t - gt0) * 1e3, what);
+    gt0 = t;
+  };
   static const char kDefault[] = "gens_r1cs_sat";  // lib.rs:475
   if (!label) { label = (const uint8_t*)kDefault; label_len = sizeof(kDefault) - 1; }
   uint64_t nvp = std::max(num_vars, num_inputs + 1), p2 = 1;  // lib.rs:467-473
@@ -451,6 +459,7 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
     work(0);
     for (auto& x : th) x.join();
   }
+  gmark("generator points (SHAKE256 + from_uniform_bytes)");
   g->G.assign(pts.begin(), pts.begin() + R);
   g->Q = pts[R];
   g->h = pts[R + 1];
@@ -512,7 +521,9 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
     int v = atoi(env);
     if (v >= 2 && v <= 16) c = (uint32_t)v;
   }
+  gmark("affine bases + window choice");
   cudaError_t ce = sb::msm_table_build(g->table, xy.data(), (uint32_t)bases.size(), c, 0);
+  gmark("device window table");
   if (ce != cudaSuccess) {
     set_error(std::string("msm_table_build: ") + cudaGetErrorString(ce));
     delete g;
@@ -527,9 +538,9 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
     FixedBase* fbs[7] = {&g->fb_G4[0], &g->fb_G4[1], &g->fb_G4[2], &g->fb_G4[3], &g->fb_h4, &g->fb_Q, &g->fb_h};
     const size_t point_of[7] = {0, 1, 2, 3, 4, (size_t)R, (size_t)R + 1};
     if (want_wide && c < 13) {
-      // narrow device windows (one-shot generators): the seven tail generators get a table of their own, 12- or 13-bit
-      // windows (30 / 55 MB), built by the same kernels and copied to the host as a whole
-      const uint32_t ch = proofs_expected > 0 && proofs_expected <= 4 ? 12 : 13;
+      // narrow device windows (one-shot generators): the seven tail generators get a table of their own, 10- or 13-bit
+      // windows (9 / 55 MB), built by the same kernels and copied to the host as a whole
+      const uint32_t ch = proofs_expected > 0 && proofs_expected <= 4 ? 10 : 13;
       std::vector<uint8_t> xy7(7 * 64);
       for (int k = 0; k < 7; k++) {
         const size_t pi = point_of[k];
@@ -545,8 +556,8 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
       cudaError_t e7 = sb::msm_table_build(t7, xy7.data(), 7, ch, 0);
       const size_t bytes = t7.entries_per_base() * (size_t)96;
       if (e7 == cudaSuccess) {
-        g->wide_store[0].resize(7 * bytes);
-        e7 = cudaMemcpy(g->wide_store[0].data(), t7.tbl, 7 * bytes, cudaMemcpyDeviceToHost);
+        g->wide_store[0].reset(new uint8_t[7 * bytes]);  // uninitialised: a vector would zero-fill what the copy overwrites
+        e7 = cudaMemcpy(g->wide_store[0].get(), t7.tbl, 7 * bytes, cudaMemcpyDeviceToHost);
       }
       sb::msm_table_free(t7);
       if (e7 != cudaSuccess) {
@@ -554,7 +565,7 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
         delete g;
         return SB200_ERR_CUDA;
       }
-      for (int k = 0; k < 7; k++) fbs[k]->set_wide(g->wide_store[0].data() + (size_t)k * bytes, ch, 252u / ch + 1u);
+      for (int k = 0; k < 7; k++) fbs[k]->set_wide(g->wide_store[0].get() + (size_t)k * bytes, ch, 252u / ch + 1u);
     } else if (want_wide) {
       const size_t bytes = g->table.entries_per_base() * (size_t)96;  // sizeof(niels_t)
       SB_CUDA(cudaDeviceSynchronize());
@@ -562,20 +573,21 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
         const size_t pi = point_of[k];
         long di = pi < R ? (long)pi : (pi == R ? (long)R + 1 : (pi == (size_t)R + 1 ? (long)R : -1));
         if (di < 0) continue;
-        g->wide_store[k].resize(bytes);
-        cudaError_t e2 = cudaMemcpy(g->wide_store[k].data(), reinterpret_cast<const uint8_t*>(g->table.tbl) + (size_t)di * bytes, bytes,
+        g->wide_store[k].reset(new uint8_t[bytes]);
+        cudaError_t e2 = cudaMemcpy(g->wide_store[k].get(), reinterpret_cast<const uint8_t*>(g->table.tbl) + (size_t)di * bytes, bytes,
                                     cudaMemcpyDeviceToHost);
         if (e2 != cudaSuccess) {
           set_error(std::string("copying a table slice to the host: ") + cudaGetErrorString(e2));
           delete g;
           return SB200_ERR_CUDA;
         }
-        fbs[k]->set_wide(g->wide_store[k].data(), g->table.c, g->table.windows);
+        fbs[k]->set_wide(g->wide_store[k].get(), g->table.c, g->table.windows);
       }
     }
     for (int k = 0; k < 7; k++)
       if (fbs[k]->wide == nullptr) fbs[k]->build(fbs[k]->point);  // cache-resident 8-bit tables (SB200_HOST_WIDE=0, or a missing slice)
   }
+  gmark("host tables of the tail generators");
   *out = reinterpret_cast<sb200_gens*>(g);
   return SB200_OK;
 }
