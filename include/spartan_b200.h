@@ -257,7 +257,7 @@ int sb200_nizk_verify(const sb200_instance* inst, const uint8_t* inputs32, uint6
  *             [12] seconds inside the exchange hook, [13] exchange calls, [14] world, [15] reserved */
 int sb200_last_prove_profile(double out[16]);
 
-/* ---- SNARK mode, first half: the computation commitment (SNARK::prove is not built).
+/* ---- SNARK mode: SNARKGens, SNARK::encode, SNARK::prove, SNARK::verify.
  * SNARKGens::new(num_cons, num_vars, num_inputs, num_nz_entries)          lib.rs:279-303
  *   only the part SNARK::encode reads: gens_r1cs_eval = R1CSCommitmentGens::new(b"gens_r1cs_eval", ...)
  *   (r1csinstance.rs:29-43, sparse_mlpoly.rs:301-327) and its window tables in HBM.  Arguments as in the reference
@@ -266,6 +266,10 @@ int sb200_last_prove_profile(double out[16]);
 typedef struct sb200_snark_gens sb200_snark_gens; /* libspartan::SNARKGens (lib.rs:273-277) */
 int sb200_snark_gens_new(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t num_nz_entries,
                          sb200_snark_gens** out);
+/* The same with the hint of sb200_gens_new_for (how many proofs the caller expects to make: window widths that
+ * minimise table build + proofs x commitments; 0 = many).  The generators do not depend on the hint. */
+int sb200_snark_gens_new_for(uint64_t num_cons, uint64_t num_vars, uint64_t num_inputs, uint64_t num_nz_entries,
+                             uint64_t proofs_expected, sb200_snark_gens** out);
 void sb200_snark_gens_free(sb200_snark_gens* gens);
 /* SNARK::encode(&inst, &gens) -> (ComputationCommitment, ComputationDecommitment)    lib.rs:321-333
  *   -> R1CSInstance::commit r1csinstance.rs:285-297 -> SparseMatPolynomial::multi_commit sparse_mlpoly.rs:485-506.
@@ -297,6 +301,32 @@ int sb200_snark_commit_derefs(const sb200_instance* inst, const sb200_snark_gens
  * layers, out[2] = product circuits.  SB200_ERR_ASSERT where the reference panics (point / memory size mismatch). */
 int sb200_snark_network_products(const sb200_instance* inst, const uint8_t* rx32, uint64_t n_rx, const uint8_t* ry32, uint64_t n_ry,
                                  const uint8_t r_hash32[32], const uint8_t r_multiset32[32], uint8_t out16[512]);
+/* SNARK::prove(&inst, &comm, &decomm, vars, &inputs, &gens, &mut transcript) -> SNARK      lib.rs:335-403
+ *   = R1CSProof::prove over gens_r1cs_sat (r1csproof.rs:141-345), inst.evaluate(rx, ry) (lib.rs:374-385), and
+ *   R1CSEvalProof::prove (r1csinstance.rs:310-329 -> SparseMatPolyEvalProof::prove, sparse_mlpoly.rs:1471-1538:
+ *   Derefs commitment, hash layers + product circuits, ProductLayerProof (the batched product-circuit sum-checks of
+ *   product_tree.rs:257-382), HashLayerProof with its three PolyEvalProofs).
+ * The commitment does not enter the prover's transcript and the decommitment (the dense representation of the matrices) is
+ * rebuilt on the device from `inst`, so neither is an argument.  transcript / label / tape_seed64 / vars32 as for
+ * sb200_nizk_prove (b"snark_example" is the label of the reference's example).  proof_out: bincode(SNARK), release with
+ * sb200_free.  SB200_ERR_ASSERT where the reference asserts or panics (generators made for other sizes, an unsatisfied
+ * memory check); SB200_ERR_ARG for a sharded instance or one with fewer than two constraints. */
+int sb200_snark_prove(const sb200_instance* inst, const sb200_snark_gens* gens, const uint8_t* vars32, uint64_t n_vars,
+                      const uint8_t* inputs32, uint64_t n_inputs, const sb200_transcript_vt* transcript, const uint8_t* label,
+                      size_t label_len, const uint8_t* tape_seed64, uint8_t** proof_out, size_t* proof_len);
+/* SNARK::verify(&self, &comm, &inputs, &mut transcript, &gens)                               lib.rs:405-457
+ *   comm: the bytes sb200_snark_encode returned (R1CSCommitment: sizes + SparseMatPolyCommitment).  Needs no instance:
+ *   R1CSProof::verify against the claimed evaluations, then R1CSEvalProof::verify (sparse_mlpoly.rs:1540-1582).  The
+ *   size-R generator MSMs of the four bullet checks run on the device, everything else on the host.
+ * 0 = accepted; SB200_ERR_PROOF_VERIFY where the reference returns Err or panics; SB200_ERR_PROOF_MALFORMED if the bytes
+ * do not parse as bincode(SNARK) / as a commitment. */
+int sb200_snark_verify(const uint8_t* comm, size_t comm_len, const sb200_snark_gens* gens, const uint8_t* inputs32, uint64_t n_inputs,
+                       const sb200_transcript_vt* transcript, const uint8_t* label, size_t label_len, const uint8_t* proof,
+                       size_t proof_len);
+/* Timer scopes of the last sb200_snark_prove, seconds (the reference's profiler lines, README.md:305-345):
+ * out[0] R1CSProof::prove, [1] eval_sparse_polys, [2] commit_nondet_witness, [3] build_layered_network,
+ * [4] product layer proofs, [5] hash layer proof ([4] + [5] = evalproof_layered_network), [6] whole call, [7] kernel launches */
+int sb200_last_snark_profile(double out[8]);
 /* milliseconds of the last sb200_snark_encode: out[0] dense representation, out[1] commitment of comb_ops,
  * out[2] commitment of comb_mem (CUDA events), out[3] the whole call on the host clock */
 int sb200_last_encode_profile(double out[4]);

@@ -6,7 +6,7 @@
 #include <chrono>
 #include <cstdlib>
 
-#include "spartan.hpp"
+#include "snark.hpp"
 
 using namespace orc;
 
@@ -262,6 +262,44 @@ int orc_snark_network_products(void* h, const uint8_t* rx, size_t nrx, const uin
     snark_network_products(((OrcInst*)h)->inst, vx, vy, rr[0], rr[1], out);
     for (int i = 0; i < 16; i++) fl_to_bytes(out[i], out16 + 32 * i);
     return 0;
+  } catch (const std::exception&) { return -1; }
+}
+
+// SNARK::prove (lib.rs:335-403): the instance handle doubles as the decommitment (R1CSDecommitment is the dense form of the same
+// matrices, rebuilt here).  Returns malloc'd bincode of SNARK.  times3 (optional): sat proof, eval proof, total seconds.
+int orc_snark_prove(void* h, size_t num_nz_entries, const uint8_t* vars, size_t nv, const uint8_t* inputs, size_t ni, const uint8_t* label,
+                    size_t ll, const uint8_t tape_seed64[64], int threads, uint8_t** out, size_t* out_len, double* times3) {
+  FlVec v, in;
+  if (!load_assign(vars, nv, v) || !load_assign(inputs, ni, in)) return InvalidScalar;
+  try {
+    const Instance& inst = ((OrcInst*)h)->inst;
+    SNARKGens gens(inst.num_cons, inst.num_vars, inst.num_inputs, num_nz_entries);
+    Transcript tr(std::string((const char*)label, ll));
+    auto t0 = std::chrono::steady_clock::now();
+    SNARK s = snark_prove(inst, v, in, gens, tr, fl_from_bytes_wide(tape_seed64), threads, times3);
+    SnarkWriter w; w.snark(s);
+    *out = (uint8_t*)malloc(w.b.size());
+    memcpy(*out, w.b.data(), w.b.size());
+    *out_len = w.b.size();
+    if (times3) times3[2] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return 0;
+  } catch (const std::exception& e) { if (getenv("ORC_VERBOSE")) fprintf(stderr, "orc_snark_prove: %s\n", e.what()); return -1; }
+}
+// SNARK::verify (lib.rs:405-457) against the commitment bytes orc_snark_encode returned.  0 = accepted, -1 = rejected, -2 = malformed
+int orc_snark_verify(const uint8_t* comm, size_t comm_len, size_t num_nz_entries, const uint8_t* inputs, size_t ni, const uint8_t* label,
+                     size_t ll, const uint8_t* proof, size_t len) {
+  FlVec in;
+  if (!load_assign(inputs, ni, in)) return InvalidScalar;
+  try {
+    Reader rc(comm, comm_len);
+    R1CSCommitment c = rc.r1cs_commitment();
+    if (!rc.ok) return -2;
+    SnarkReader r(proof, len);
+    SNARK s = r.snark();
+    if (!r.ok) return -2;
+    SNARKGens gens(c.num_cons, c.num_vars, c.num_inputs, num_nz_entries);
+    Transcript tr(std::string((const char*)label, ll));
+    return snark_verify(s, c, in, gens, tr) ? 0 : -1;
   } catch (const std::exception&) { return -1; }
 }
 void orc_free(void* p) { free(p); }

@@ -698,19 +698,14 @@ static inline FlVec poly_bound(const FlVec& Z, const FlVec& Lv, size_t R) {
 
 struct PhaseTimes { double polycommit, phase1, phase2, polyeval, total; };
 
-// NIZK::prove lib.rs:493-535 + R1CSProof::prove r1csproof.rs:141-345
-static inline NIZK nizk_prove(const Instance& inst, const FlVec& vars_in, const FlVec& inputs, const NIZKGens& gens,
-                              Transcript& tr, const Fl& tape_seed, int threads = 1, PhaseTimes* times = nullptr) {
+// R1CSProof::prove r1csproof.rs:141-345 (shared by NIZK::prove and SNARK::prove; `vars` already padded).  Returns the proof, rx, ry.
+static inline R1CSProof r1cs_prove(const Instance& inst, const FlVec& vars, const FlVec& inputs, const NIZKGens& gens, Transcript& tr,
+                                   RandomTape& tape, int threads, FlVec& rx, FlVec& ry, PhaseTimes* times = nullptr) {
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   double t0 = now();
-  RandomTape tape("proof", tape_seed);
-  tr.append_protocol_name("Spartan NIZK proof");
-  FlVec vars = vars_in;
-  if (inst.num_vars > vars.size()) vars.resize(inst.num_vars, fl_zero());  // Assignment::pad, lib.rs:92-105
   tr.append_protocol_name("R1CS proof");
   if (!(inputs.size() < vars.size())) throw std::runtime_error("assert input.len() < vars.len()");  // r1csproof.rs:153
-  NIZK out;
-  R1CSProof& pf = out.r1cs_sat_proof;
+  R1CSProof pf;
   size_t nv = vars.size(), ell = ilog2(nv), lnv = ell / 2, Ls = size_t(1) << lnv, Rs = size_t(1) << (ell - lnv);
   // polycommit, dense_mlpoly.rs:178-203
   FlVec blinds_vars = tape.random_vector("poly_blinds", Ls);
@@ -728,7 +723,7 @@ static inline NIZK nizk_prove(const Instance& inst, const FlVec& vars_in, const 
   FlVec tau = tr.challenge_vector("challenge_tau", nrx);
   FlVec poly_tau = eq_evals(tau);
   FlVec Az = inst.multiply_vec(0, z), Bz = inst.multiply_vec(1, z), Cz = inst.multiply_vec(2, z);
-  FlVec rx, claims1;
+  FlVec claims1;
   Fl blind_post1;
   pf.sc_proof_phase1 = zk_sumcheck_prove(fl_zero(), fl_zero(), nrx, {&poly_tau, &Az, &Bz, &Cz}, 3, gens.gens_1,
                                          gens.gens_4, tr, tape, rx, claims1, blind_post1);
@@ -760,7 +755,7 @@ static inline NIZK nizk_prove(const Instance& inst, const FlVec& vars_in, const 
   FlVec evals_ABC(z.size());
   for (size_t i = 0; i < z.size(); i++)
     evals_ABC[i] = fl_add(fl_add(fl_mul(r_A, eA[i]), fl_mul(r_B, eB[i])), fl_mul(r_C, eC[i]));
-  FlVec zz = z, ry, claims2;
+  FlVec zz = z, claims2;
   Fl blind_post2;
   pf.sc_proof_phase2 = zk_sumcheck_prove(claim2, blind2, nry, {&zz, &evals_ABC}, 2, gens.gens_1, gens.gens_3, tr, tape,
                                          ry, claims2, blind_post2);
@@ -782,9 +777,18 @@ static inline NIZK nizk_prove(const Instance& inst, const FlVec& vars_in, const 
   Fl blind_exp2 = fl_mul(claims2[1], blind_eval_Z);
   Fl claim_post2 = fl_mul(claims2[0], claims2[1]);
   pf.proof_eq_sc_phase2 = equality_prove(gens.gens_1, tr, tape, claim_post2, blind_exp2, claim_post2, blind_post2);
-  out.rx = rx;
-  out.ry = ry;
   if (times) { times->polycommit = t1 - t0; times->phase1 = t2 - t1; times->phase2 = t3 - t2; times->polyeval = t4 - t3; times->total = now() - t0; }
+  return pf;
+}
+// NIZK::prove lib.rs:493-535
+static inline NIZK nizk_prove(const Instance& inst, const FlVec& vars_in, const FlVec& inputs, const NIZKGens& gens,
+                              Transcript& tr, const Fl& tape_seed, int threads = 1, PhaseTimes* times = nullptr) {
+  RandomTape tape("proof", tape_seed);
+  tr.append_protocol_name("Spartan NIZK proof");
+  FlVec vars = vars_in;
+  if (inst.num_vars > vars.size()) vars.resize(inst.num_vars, fl_zero());  // Assignment::pad, lib.rs:92-105
+  NIZK out;
+  out.r1cs_sat_proof = r1cs_prove(inst, vars, inputs, gens, tr, tape, threads, out.rx, out.ry, times);
   return out;
 }
 
@@ -804,14 +808,10 @@ static inline Fl sparse_poly_evaluate(size_t num_vars, const std::vector<std::pa
 
 // NIZK::verify lib.rs:538-574 + R1CSProof::verify r1csproof.rs:347-498.
 // The reference's asserts/unwraps (panics) become `false` here.
-static inline bool nizk_verify_inner(const NIZK& nz, const Instance& inst, const FlVec& inputs, const NIZKGens& gens,
-                                     Transcript& tr) {
-  const R1CSProof& pf = nz.r1cs_sat_proof;
-  tr.append_protocol_name("Spartan NIZK proof");
-  if (nz.rx.size() != ilog2(inst.num_cons) || nz.ry.size() != ilog2(2 * inst.num_vars)) return false;
-  Fl ev[3];
-  inst.evaluate(nz.rx, nz.ry, ev);
-  if (inputs.size() != inst.num_inputs) return false;
+// R1CSProof::verify r1csproof.rs:347-498: `ev` = the claimed (A, B, C)(rx, ry); returns the rx, ry of the two sum-checks
+static inline bool r1cs_verify(const R1CSProof& pf, size_t num_vars, size_t num_cons, const FlVec& inputs, const Fl ev[3],
+                               const NIZKGens& gens, Transcript& tr, FlVec& rx, FlVec& ry) {
+  struct { size_t num_cons, num_vars; } inst{num_cons, num_vars};
   tr.append_protocol_name("R1CS proof");
   size_t n = inst.num_vars;
   tr.append_message("poly_commitment", "poly_commitment_begin");
@@ -821,7 +821,6 @@ static inline bool nizk_verify_inner(const NIZK& nz, const Instance& inst, const
   FlVec tau = tr.challenge_vector("challenge_tau", nrx);
   CPt claim1 = compress(commit_scalar(fl_zero(), fl_zero(), gens.gens_1));
   CPt comm_post1, comm_post2;
-  FlVec rx, ry;
   if (!zk_sumcheck_verify(pf.sc_proof_phase1, claim1, nrx, 3, gens.gens_1, gens.gens_4, tr, comm_post1, rx)) return false;
   const CPt &comm_Az = pf.claims_phase2[0], &comm_Bz = pf.claims_phase2[1], &comm_Cz = pf.claims_phase2[2],
             &comm_prod = pf.claims_phase2[3];
@@ -863,7 +862,17 @@ static inline bool nizk_verify_inner(const NIZK& nz, const Instance& inst, const
   Pt comm_eval_Z = pt_msm(ws, ps, 2);
   Fl k = fl_add(fl_add(fl_mul(r_A, ev[0]), fl_mul(r_B, ev[1])), fl_mul(r_C, ev[2]));
   CPt exp2 = compress(pt_mul(k, comm_eval_Z));
-  if (!equality_verify(pf.proof_eq_sc_phase2, gens.gens_1, tr, exp2, comm_post2)) return false;
+  return equality_verify(pf.proof_eq_sc_phase2, gens.gens_1, tr, exp2, comm_post2);
+}
+static inline bool nizk_verify_inner(const NIZK& nz, const Instance& inst, const FlVec& inputs, const NIZKGens& gens,
+                                     Transcript& tr) {  // lib.rs:538-574
+  tr.append_protocol_name("Spartan NIZK proof");
+  if (nz.rx.size() != ilog2(inst.num_cons) || nz.ry.size() != ilog2(2 * inst.num_vars)) return false;
+  Fl ev[3];
+  inst.evaluate(nz.rx, nz.ry, ev);
+  if (inputs.size() != inst.num_inputs) return false;
+  FlVec rx, ry;
+  if (!r1cs_verify(nz.r1cs_sat_proof, inst.num_vars, inst.num_cons, inputs, ev, gens, tr, rx, ry)) return false;
   return rx == nz.rx && ry == nz.ry;
 }
 static inline bool nizk_verify(const NIZK& nz, const Instance& inst, const FlVec& inputs, const NIZKGens& gens,
@@ -1158,9 +1167,8 @@ struct Reader {
     return s;
   }
   EqualityProof eq() { EqualityProof e; e.alpha = pt(); e.z = fl(); return e; }
-  NIZK nizk() {
-    NIZK nz;
-    R1CSProof& q = nz.r1cs_sat_proof;
+  R1CSProof r1cs() {
+    R1CSProof q;
     q.comm_vars = pts(); q.sc_proof_phase1 = sc();
     for (int i = 0; i < 4; i++) q.claims_phase2[i] = pt();
     q.pok_Cz.alpha = pt(); q.pok_Cz.z1 = fl(); q.pok_Cz.z2 = fl();
@@ -1170,9 +1178,22 @@ struct Reader {
     DotProductProofLog& d = q.proof_eval_vars_at_ry;
     d.bullet.L_vec = pts(); d.bullet.R_vec = pts(); d.delta = pt(); d.beta = pt(); d.z1 = fl(); d.z2 = fl();
     q.proof_eq_sc_phase2 = eq();
+    return q;
+  }
+  NIZK nizk() {
+    NIZK nz;
+    nz.r1cs_sat_proof = r1cs();
     nz.rx = fls(); nz.ry = fls();
     if (pos != n) ok = false;
     return nz;
+  }
+  R1CSCommitment r1cs_commitment() {
+    R1CSCommitment c;
+    c.num_cons = u64(); c.num_vars = u64(); c.num_inputs = u64();
+    c.comm.batch_size = u64(); c.comm.num_ops = u64(); c.comm.num_mem_cells = u64();
+    c.comm.comm_comb_ops = pts(); c.comm.comm_comb_mem = pts();
+    if (pos != n) ok = false;
+    return c;
   }
 };
 

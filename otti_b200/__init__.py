@@ -350,14 +350,18 @@ class SNARKGens:
     """`SNARKGens::new(num_cons, num_vars, num_inputs, num_nz_entries)` (lib.rs:279-303) -- the generators
     SNARK::encode reads (`gens_r1cs_eval`) and their window tables in HBM."""
 
-    def __init__(self, num_cons, num_vars, num_inputs, num_nz_entries):
+    def __init__(self, num_cons, num_vars, num_inputs, num_nz_entries, proofs_expected=None):
         self.h = C.c_void_p()
-        _check(lib().sb200_snark_gens_new(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
-                                          C.c_uint64(num_nz_entries), C.byref(self.h)))
+        if proofs_expected is None:
+            _check(lib().sb200_snark_gens_new(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
+                                              C.c_uint64(num_nz_entries), C.byref(self.h)))
+        else:
+            _check(lib().sb200_snark_gens_new_for(C.c_uint64(num_cons), C.c_uint64(num_vars), C.c_uint64(num_inputs),
+                                                  C.c_uint64(num_nz_entries), C.c_uint64(proofs_expected), C.byref(self.h)))
 
     @staticmethod
-    def new(num_cons, num_vars, num_inputs, num_nz_entries):
-        return SNARKGens(num_cons, num_vars, num_inputs, num_nz_entries)
+    def new(num_cons, num_vars, num_inputs, num_nz_entries, proofs_expected=None):
+        return SNARKGens(num_cons, num_vars, num_inputs, num_nz_entries, proofs_expected)
 
     def __del__(self):
         if getattr(self, "h", None) and _lib is not None:
@@ -388,7 +392,52 @@ class ComputationCommitment:
 
 
 class SNARK:
-    """SNARK mode (lib.rs:305-457).  Only the public preprocessing step is built; `prove` / `verify` are not."""
+    """`SNARK` (lib.rs:305-457).  An object holds bincode(SNARK) exactly as the reference would serialise it; the static
+    methods below `verify` are the steps of `prove` exposed one by one (tests, profiling)."""
+
+    def __init__(self, proof_bytes=b""):
+        self.bytes = proof_bytes
+
+    @staticmethod
+    def prove(inst, comm, decomm, vars_, inputs, gens, transcript, tape_seed64=None, resident=False):
+        """`SNARK::prove(&inst, &comm, &decomm, vars, &inputs, &gens, &mut transcript)` (lib.rs:335-403).  `comm` and
+        `decomm` are accepted for signature parity and unused: the commitment does not enter the prover's transcript and
+        the decommitment is rebuilt on the device from `inst`."""
+        vp, vk = (None, None) if resident else _ptr(vars_.data)
+        ip, ik = _ptr(inputs.data)
+        sp, sk = _ptr(tape_seed64)
+        if tape_seed64 is not None and len(tape_seed64) != 64:
+            raise ValueError("tape_seed64 must be 64 bytes")
+        vt = transcript._vt()
+        out = C.POINTER(C.c_uint8)()
+        n = C.c_size_t(0)
+        _check(lib().sb200_snark_prove(inst.h, gens.h, vp, C.c_uint64(vars_.n), ip, C.c_uint64(inputs.n), C.byref(vt), None,
+                                       C.c_size_t(0), sp, C.byref(out), C.byref(n)))
+        b = C.string_at(out, n.value)
+        lib().sb200_free(out)
+        return SNARK(b)
+
+    def verify(self, comm, inputs, transcript, gens):
+        """`SNARK::verify(&self, &comm, &inputs, &mut transcript, &gens)` (lib.rs:405-457).  Returns None on success,
+        raises ProofVerifyError otherwise."""
+        cb = comm.to_bytes() if hasattr(comm, "to_bytes") else comm
+        cp, ck = _ptr(cb)
+        ip, ik = _ptr(inputs.data)
+        pp, pk = _ptr(self.bytes)
+        vt = transcript._vt()
+        _check(lib().sb200_snark_verify(cp, C.c_size_t(len(cb)), gens.h, ip, C.c_uint64(inputs.n), C.byref(vt), None, C.c_size_t(0),
+                                        pp, C.c_size_t(len(self.bytes))))
+
+    def to_bytes(self):
+        return self.bytes
+
+    @staticmethod
+    def last_prove_profile():
+        """Timer scopes of the last `prove`, seconds (the reference's profiler lines, README.md:305-345)."""
+        d = (C.c_double * 8)()
+        lib().sb200_last_snark_profile(d)
+        return dict(zip(["r1cs_sat_proof", "eval_sparse_polys", "commit_nondet_witness", "build_layered_network",
+                         "product_layer_proof", "hash_layer_proof", "total", "kernel_launches"], list(d)))
 
     @staticmethod
     def encode(inst, gens):

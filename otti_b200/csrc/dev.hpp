@@ -143,6 +143,10 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
 // LZ[i] = sum_j Lv[j] * Z[j*R + i]                                    (dense_mlpoly.rs:205-212)
 cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rsize, fl_t* out, fl_t* tmp,
                       cudaStream_t s);
+// the same for a polynomial stored as canonical integers (comb_ops, comb_mem, Derefs.comb): Montgomery Lv times canonical Z
+// sums to the canonical LZ (out_canon: the MSM's input form); out_mont receives its Montgomery form
+cudaError_t k_bound_L_canon(const fl_t* Z_canon, const fl_t* Lv, uint32_t Lsize, uint32_t Rsize, fl_t* out_canon, fl_t* out_mont,
+                            fl_t* tmp, cudaStream_t s);
 size_t bound_L_tmp_scalars(uint32_t Lsize, uint32_t Rsize);
 // out[0] = <a, b>   (n <= 2^16, one block)                            (nizk/mod.rs:305-308)
 cudaError_t k_dot_small(const fl_t* a, const fl_t* b, uint32_t n, fl_t* out, cudaStream_t s);
@@ -152,11 +156,45 @@ cudaError_t k_dot3(const fl_t* e, const fl_t* yA, const fl_t* yB, const fl_t* yC
 
 // Bullet reduction scalar side (nizk/bullet.rs:71-118), see kernels.cu
 // (a_in, b_in) are read only; with do_fold the folded vectors go to (a_out, b_out) -- a different pair of buffers
+// pos_h / pos_q: where a row keeps the scalars of H (blind) and Q (inner product) -- the positions of those two bases in
+// the window table; 0 = the table of a NIZKGens ([R] = H, [R+1] = Q)
 cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t* b_out, const fl_t* coeff_in, fl_t* coeff_out,
                           uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL,
-                          fl_t* sR, cudaStream_t s);
+                          fl_t* sR, cudaStream_t s, uint32_t pos_h = 0, uint32_t pos_q = 0);
 // s[g] = from_mont(d * coeff[g]) for g < R                            (nizk/mod.rs:483-490)
 cudaError_t k_scale_from_mont(const fl_t* coeff, fl_t d, uint32_t n, fl_t* out, cudaStream_t s);
+
+// ---- SNARK::prove: the batched sum-checks of ProductCircuitEvalProofBatched (product_tree.rs:257-382) -----------------
+// Instance k of a layer: tables A_k, B_k (left / right half of a product-circuit layer, or left / right of a dot-product
+// circuit) and C_k = the instance's own weight table, or NULL for the eq table all product circuits share (Cin; with a
+// bind its bound form is written to Cout, a different buffer, by the units of instance `cwriter`).
+static constexpr int kPcMax = 18;
+struct PcBatch {
+  fl_t* A[kPcMax];
+  fl_t* B[kPcMax];
+  fl_t* C[kPcMax];
+  fl_t coeff[kPcMax];  // rand_coeffs_next_layer, Montgomery
+  const fl_t* Cin;
+  fl_t* Cout;
+  uint32_t ninst, cwriter;
+};
+// One round of SumcheckInstanceProof::prove_cubic_batched (sumcheck.rs:252-422) on tables of length n_old: if do_bind
+// every table is first bound at r (-> n_old / 2); then the round's combined evaluations at 0, 2, 3 go to w.result and
+// the mailbox.  Lengths are powers of two, length after the bind >= 2.
+cudaError_t k_pc_round(const PcBatch& b, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s);
+// host_out[3k + t] = final value of table t (A, B, own C / zero) of instance k, after a last bind at r if do_bind
+cudaError_t k_pc_final(const PcBatch& b, bool do_bind, fl_t r, fl_t* host_out, uint32_t* host_flag, uint32_t seq, cudaStream_t s);
+// out[j] = sum_i X_j[i] * Y_j[i] (* W_j[i] if W_j != NULL), j < nvec; tmp: multi_dot_tmp_scalars(nvec).
+// final_to_mont: Y canonical integers -> the sum is canonical, converted to Montgomery at the end.
+static constexpr int kDotMax = 24;
+struct DotBatch {
+  const fl_t* X[kDotMax];
+  const fl_t* Y[kDotMax];
+  const fl_t* W[kDotMax];
+  uint32_t nvec;
+};
+size_t multi_dot_tmp_scalars(uint32_t nvec);
+cudaError_t k_multi_dot(const DotBatch& b, size_t n, bool final_to_mont, fl_t* tmp, fl_t* out, cudaStream_t s);
 
 // per-kernel device time of every launch while enabled (CUDA events around each launch); report = CSV lines
 // "kernel,launches,total_ms" sorted by time, and clears the records

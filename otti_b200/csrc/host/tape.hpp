@@ -31,8 +31,13 @@ struct TapeLayout {
   size_t dlog;                         // d, r_delta, r_beta (label "r_delta", sic)  nizk/mod.rs:452-454
   size_t bv1, bv2;                     // 2 lgR each                 nizk/mod.rs:456-457
   size_t eq2_r;
+  // SNARK::prove continues on the same tape: one DotProductProofLog::prove draw sequence (d, r_delta, r_beta, 2 lg n
+  // blinds_vec_1, 2 lg n blinds_vec_2) per polynomial evaluation proof of the R1CSEvalProof, in proving order
+  // (derefs, ops, mem: sparse_mlpoly.rs:723-837); extra_lg[k] = lg n of proof k, extra_off[k] its first draw
+  std::vector<size_t> extra_lg, extra_off;
   size_t total;
-  TapeLayout(size_t Ls_, size_t s_x_, size_t s_y_, size_t lgR_) : Ls(Ls_), s_x(s_x_), s_y(s_y_), lgR(lgR_) {
+  TapeLayout(size_t Ls_, size_t s_x_, size_t s_y_, size_t lgR_, const std::vector<size_t>& extra = {})
+      : Ls(Ls_), s_x(s_x_), s_y(s_y_), lgR(lgR_), extra_lg(extra) {
     size_t o = 0;
     poly_blinds = o; o += Ls;
     sc1_blinds_poly = o; o += s_x;
@@ -50,6 +55,7 @@ struct TapeLayout {
     bv1 = o; o += 2 * lgR;
     bv2 = o; o += 2 * lgR;
     eq2_r = o; o += 1;
+    for (size_t lg : extra_lg) { extra_off.push_back(o); o += 3 + 4 * lg; }
     total = o;
   }
 };
@@ -90,6 +96,11 @@ class TapeAhead {
     draw("blinds_vec_1", 2 * lay.lgR, k);
     draw("blinds_vec_2", 2 * lay.lgR, k);
     draw("r", 1, k);
+    for (size_t lg : lay.extra_lg) {
+      draw("d", 1, k); draw("r_delta", 1, k); draw("r_delta", 1, k);
+      draw("blinds_vec_1", 2 * lg, k);
+      draw("blinds_vec_2", 2 * lg, k);
+    }
   }
   // value #i of the sequence; waits until the drawing thread has produced it
   const Fl& at(size_t i) const {

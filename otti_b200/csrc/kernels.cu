@@ -720,7 +720,8 @@ __global__ void bound_partial_kernel(const fl_t* __restrict__ Z, const fl_t* __r
   for (uint32_t j = j0; j < j1; j++) acc = fl_add(acc, fl_mul(ldg_fl(Lv + j), ldg_fl(Z + (size_t)j * Rsize + i)));
   st_fl(tmp + (size_t)blockIdx.y * Rsize + i, acc);
 }
-__global__ void bound_sum_kernel(const fl_t* __restrict__ tmp, uint32_t Rsize, uint32_t jc, fl_t* __restrict__ out) {
+__global__ void bound_sum_kernel(const fl_t* __restrict__ tmp, uint32_t Rsize, uint32_t jc, fl_t* __restrict__ out,
+                                 fl_t* __restrict__ out_mont = nullptr) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Rsize) return;
   // four independent partial sums: the loads of a step do not wait for the previous step's addition
@@ -736,7 +737,9 @@ __global__ void bound_sum_kernel(const fl_t* __restrict__ tmp, uint32_t Rsize, u
     for (int k = 0; k < 4; k++) acc[k] = fl_add(acc[k], v[k]);
   }
   for (; c < jc; c++) acc[0] = fl_add(acc[0], ldg_fl(tmp + (size_t)c * Rsize + i));
-  st_fl(out + i, fl_add(fl_add(acc[0], acc[1]), fl_add(acc[2], acc[3])));
+  const fl_t tot = fl_add(fl_add(acc[0], acc[1]), fl_add(acc[2], acc[3]));
+  st_fl(out + i, tot);
+  if (out_mont != nullptr) st_fl(out_mont + i, fl_to_mont(tot));
 }
 // chunks of rows: enough blocks for ~8 per SM, but few enough (<= 64) that the second pass stays short
 static inline uint32_t bound_chunks(uint32_t Lsize, uint32_t Rsize) {
@@ -756,6 +759,17 @@ cudaError_t k_bound_L(const fl_t* Z, const fl_t* Lv, uint32_t Lsize, uint32_t Rs
   cudaError_t e = SB_LAUNCHED();
   if (e != cudaSuccess) return e;
   { KProf kp_("bound_sum_kernel", s); bound_sum_kernel<<<(Rsize + 127) / 128, 128, 0, s>>>(tmp, Rsize, jc, out); }
+  return SB_LAUNCHED();
+}
+cudaError_t k_bound_L_canon(const fl_t* Z_canon, const fl_t* Lv, uint32_t Lsize, uint32_t Rsize, fl_t* out_canon, fl_t* out_mont,
+                            fl_t* tmp, cudaStream_t s) {
+  uint32_t jc = bound_chunks(Lsize, Rsize), jper = (Lsize + jc - 1) / jc;
+  jc = (Lsize + jper - 1) / jper;
+  dim3 grid((Rsize + 127) / 128, jc);
+  { KProf kp_("bound_partial_kernel", s); bound_partial_kernel<<<grid, 128, 0, s>>>(Z_canon, Lv, Lsize, Rsize, jper, tmp); }
+  cudaError_t e = SB_LAUNCHED();
+  if (e != cudaSuccess) return e;
+  { KProf kp_("bound_sum_kernel", s); bound_sum_kernel<<<(Rsize + 127) / 128, 128, 0, s>>>(tmp, Rsize, jc, out_canon, out_mont); }
   return SB_LAUNCHED();
 }
 __global__ void dot_small_kernel(const fl_t* __restrict__ a, const fl_t* __restrict__ b, uint32_t n, fl_t* out) {
@@ -813,7 +827,8 @@ __global__ void __launch_bounds__(kBulletThreads) bullet_step_kernel(const fl_t*
                                                                      fl_t* __restrict__ a_out, fl_t* __restrict__ b_out,
                                                                      const fl_t* __restrict__ coeff_in, fl_t* __restrict__ coeff_out,
                                                                      uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv,
-                                                                     fl_t blind_L, fl_t blind_R, fl_t* __restrict__ sL, fl_t* __restrict__ sR) {
+                                                                     fl_t blind_L, fl_t blind_R, fl_t* __restrict__ sL, fl_t* __restrict__ sR,
+                                                                     uint32_t pos_h, uint32_t pos_q) {
   __shared__ fl_t smem[2 * 32];
   const uint32_t n = do_fold ? n_cur / 2 : n_cur, half = n / 2;
   if (blockIdx.x + 1 < gridDim.x) {  // row block: the two MSM scalar rows over the ORIGINAL bases
@@ -862,19 +877,20 @@ __global__ void __launch_bounds__(kBulletThreads) bullet_step_kernel(const fl_t*
   block_sum_fl<2>(c, smem);
   if (threadIdx.x < 4) {  // rows have stride R + 2: [R] = H (blind), [R + 1] = Q (inner product); canonical form
     const fl_t v = threadIdx.x == 0 ? blind_L : threadIdx.x == 1 ? blind_R : fl_zero();
-    if (threadIdx.x < 2) st_fl((threadIdx.x == 0 ? sL : sR) + Rsize, fl_from_mont_c(v));
+    if (threadIdx.x < 2) st_fl((threadIdx.x == 0 ? sL : sR) + pos_h, fl_from_mont_c(v));
     if (threadIdx.x == 0) {
-      st_fl(sL + Rsize + 1, fl_from_mont_c(c[0]));
-      st_fl(sR + Rsize + 1, fl_from_mont_c(c[1]));
+      st_fl(sL + pos_q, fl_from_mont_c(c[0]));
+      st_fl(sR + pos_q, fl_from_mont_c(c[1]));
     }
   }
 }
 cudaError_t k_bullet_step(const fl_t* a_in, const fl_t* b_in, fl_t* a_out, fl_t* b_out, const fl_t* coeff_in, fl_t* coeff_out,
                           uint32_t n_cur, uint32_t Rsize, bool do_fold, fl_t u, fl_t u_inv, fl_t blind_L, fl_t blind_R, fl_t* sL,
-                          fl_t* sR, cudaStream_t s) {
+                          fl_t* sR, cudaStream_t s, uint32_t pos_h, uint32_t pos_q) {
   const unsigned row_blocks = (Rsize + kBulletThreads - 1) / kBulletThreads;
+  if (pos_h == 0 && pos_q == 0) { pos_h = Rsize; pos_q = Rsize + 1; }
   { KProf kp_("bullet_step_kernel", s); bullet_step_kernel<<<row_blocks + 1, kBulletThreads, 0, s>>>(a_in, b_in, a_out, b_out, coeff_in, coeff_out, n_cur, Rsize, do_fold, u, u_inv,
-                                                              blind_L, blind_R, sL, sR); }
+                                                              blind_L, blind_R, sL, sR, pos_h, pos_q); }
   return SB_LAUNCHED();
 }
 __global__ void scale_from_mont_kernel(const fl_t* __restrict__ coeff, fl_t d, uint32_t n, fl_t* __restrict__ out) {
@@ -1098,6 +1114,8 @@ cudaError_t k_prod_trees(fl_t* const bufs[], const uint32_t lens[], int ntrees, 
   { KProf kp_("prod_tail_kernel", s); prod_tail_kernel<<<ntrees, 512, 0, s>>>(t, tail, products); }
   return SB_LAUNCHED();
 }
+
+#include "snark_kernels.inc"
 
 // ------------------------------------------------------------------ fixed-base MSM
 __device__ __forceinline__ niels_t ldg_niels(const niels_t* p) {

@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <random>
 #include <thread>
@@ -889,3 +890,4 @@ int sb200_last_prove_profile(double out[16]) {
 #include "verify.inc"
 #include "kernel_hooks.inc"
 #include "snark.inc"
+#include "snark_prove.inc"

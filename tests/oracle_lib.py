@@ -16,7 +16,7 @@ u8p = C.POINTER(C.c_uint8)
 
 def build(force=False):
     srcs = [os.path.join(_ROOT, "oracle", f) for f in
-            ("oracle_capi.cpp", "spartan.hpp", "transcript.hpp", "ristretto.hpp", "fl.hpp")]
+            ("oracle_capi.cpp", "spartan.hpp", "snark.hpp", "transcript.hpp", "ristretto.hpp", "fl.hpp")]
     if force or not os.path.exists(_SO) or any(os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(["make", "-C", os.path.join(_ROOT, "oracle")], stdout=subprocess.DEVNULL)
     return _SO
@@ -381,3 +381,25 @@ def snark_network_products(inst, rx_canon, ry_canon, r_hash_canon, r_multiset_ca
         raise RuntimeError("oracle network products failed: %d" % rc)
     b = bytes(out)
     return [b[32 * i:32 * i + 32] for i in range(16)]
+
+
+def snark_prove(inst, num_nz_entries, vars_b, inputs_b, label, tape_seed64, threads=1, want_times=False):
+    """SNARK::prove (lib.rs:335-403): bincode of SNARK { r1cs_sat_proof, inst_evals, r1cs_eval_proof }."""
+    out = u8p()
+    n = C.c_size_t(0)
+    t = (C.c_double * 3)()
+    rc = lib().orc_snark_prove(inst.h, C.c_size_t(num_nz_entries), _buf(vars_b), C.c_size_t(len(vars_b) // 32), _buf(inputs_b),
+                               C.c_size_t(len(inputs_b) // 32), _buf(label), C.c_size_t(len(label)), _buf(tape_seed64), threads,
+                               C.byref(out), C.byref(n), t)
+    if rc != 0:
+        raise RuntimeError("oracle SNARK::prove failed: %d" % rc)
+    b = C.string_at(out, n.value)
+    lib().orc_free(out)
+    return (b, list(t)) if want_times else b
+
+
+def snark_verify(comm, num_nz_entries, inputs_b, label, proof):
+    """SNARK::verify (lib.rs:405-457) against the bytes snark_encode returned.  0 accepted, -1 rejected, -2 malformed."""
+    return lib().orc_snark_verify(_buf(comm), C.c_size_t(len(comm)), C.c_size_t(num_nz_entries), _buf(inputs_b),
+                                  C.c_size_t(len(inputs_b) // 32), _buf(label), C.c_size_t(len(label)), _buf(proof),
+                                  C.c_size_t(len(proof)))
