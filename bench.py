@@ -447,8 +447,8 @@ def side_otti(env, s):
 
 
 def snark_side_measurements(sb, inst, n, s):
-    """The parts of SNARK mode that are built, on a 2^16 instance, outside the timed region of the
-    headline metric: whole-call milliseconds (best of 4) of each call.  Never fails the bench line."""
+    """SNARK mode on a 2^16 instance, outside the timed region of the headline metric: whole-call
+    milliseconds (best of 4) of each step, then SNARK::prove / verify.  Never fails the bench line."""
     try:
         import random
         rng = random.Random(s)
@@ -479,8 +479,72 @@ def snark_side_measurements(sb, inst, n, s):
         return {"error": "%s: %s" % (type(e).__name__, e)}
 
 
-def snark_prove_measurements(sb, inst, gens, n, s):
-    return {}
+SNARK_LABEL = b"snark_example"
+
+
+def snark_prove_measurements(sb, inst, gens, n, s, vars_=None, inputs=None, oracle_check=True):
+    """SNARK::prove / SNARK::verify (lib.rs:335-457) on the resident instance: wall-clock milliseconds of the calls (host
+    buffers in, proof bytes out), the scopes of the reference's profiler, the proof against the CPU restatement."""
+    import statistics
+    if vars_ is None:
+        _, vars_, inputs = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED)
+    comm = sb.SNARK.encode(inst, gens)
+    proof = None
+    for _ in range(2):
+        proof = sb.SNARK.prove(inst, comm, None, vars_, inputs, gens, sb.Transcript.new(SNARK_LABEL), TAPE)
+    ts, profs = [], []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        proof = sb.SNARK.prove(inst, comm, None, vars_, inputs, gens, sb.Transcript.new(SNARK_LABEL), TAPE)
+        ts.append(1e3 * (time.perf_counter() - t0))
+        profs.append(sb.SNARK.last_prove_profile())
+    tv = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        proof.verify(comm, inputs, sb.Transcript.new(SNARK_LABEL), gens)
+        tv.append(1e3 * (time.perf_counter() - t0))
+    best = profs[ts.index(min(ts))]
+    out = {"prove_ms": round(statistics.median(ts), 3), "prove_ms_min": round(min(ts), 3), "verify_ms": round(statistics.median(tv), 3),
+           "proof_bytes": len(proof.to_bytes()), "kernel_launches_per_proof": int(best["kernel_launches"]),
+           "prove_scopes_ms": {k: round(1e3 * best[k], 3) for k in ("r1cs_sat_proof", "eval_sparse_polys", "commit_nondet_witness",
+                                                                    "build_layered_network", "product_layer_proof", "hash_layer_proof")}}
+    if oracle_check:
+        import oracle_lib as O
+        oi, ov, oin = O.Instance.synthetic(n, n, NUM_INPUTS, SEED)
+        threads = host_threads()
+        t0 = time.perf_counter()
+        want = O.snark_prove(oi, n, ov, oin, SNARK_LABEL, TAPE, threads=threads)
+        t1 = time.perf_counter()
+        ok = O.snark_verify(comm.to_bytes(), n, oin, SNARK_LABEL, proof.to_bytes()) == 0
+        t2 = time.perf_counter()
+        out["cpu_port"] = {"prove_s": round(t1 - t0, 3), "verify_s": round(t2 - t1, 3), "cores": threads,
+                           "proof_bytes_equal_gpu": want == proof.to_bytes(), "oracle_verify_accepts_gpu_proof": ok}
+    return out
+
+
+def side_snark_2p20(env):
+    """SNARK mode at the size the reference publishes its profile for (README.md:305-345: 2^20 constraints, variables and
+    non-zero entries per matrix): encode, prove, verify through the public API."""
+    sb, torch = env.sb, env.torch
+    s, n = 20, 1 << 20
+    inst, vars_, inputs = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED, pinned=True)
+    t0 = time.perf_counter()
+    gens = sb.SNARKGens.new(n, n, NUM_INPUTS, n)
+    torch.cuda.synchronize()
+    out = {"workload": "synthetic R1CS 2^20 (constraints = variables = non-zero entries per matrix), SNARK mode",
+           "gens_build_s_untimed": round(time.perf_counter() - t0, 3)}
+    best = None
+    for _ in range(3):
+        sb.SNARK.encode(inst, gens)
+        p = sb.SNARK.last_encode_profile()
+        best = p if best is None or p["total_ms"] < best["total_ms"] else best
+    out["encode_ms"] = round(best["total_ms"], 3)
+    out.update(snark_prove_measurements(sb, inst, gens, n, s, vars_, inputs, oracle_check=not env.args.no_cpu_baseline))
+    out["published_reference"] = {"encode_s": 14.26, "prove_s": 39.13, "r1cs_sat_proof_s": 4.44, "eval_sparse_polys_s": 0.377,
+                                  "commit_nondet_witness_s": 14.45, "build_layered_network_s": 3.44, "evalproof_layered_network_s": 15.57,
+                                  "proof_bytes": 47024 + 96 + 133720,
+                                  "note": "Spartan/README.md:305-345, 1 core i7-1065G7 (other hardware; not the same measurement)"}
+    return out
 
 
 def run_sharded(env, s):
@@ -701,6 +765,11 @@ def main():
                 line["snark_mode"] = snark
         except Exception as e:
             side["synthetic_2p16"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        if not args.no_snark:
+            try:
+                side["snark_2p20"] = side_snark_2p20(env)
+            except Exception as e:
+                side["snark_2p20"] = {"error": "%s: %s" % (type(e).__name__, e)}
         try:
             side["otti_shaped"] = side_otti(env, args.otti_log_size)
         except Exception as e:
