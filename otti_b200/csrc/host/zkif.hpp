@@ -5,12 +5,15 @@
 // No flatc here, so the reader walks the wire format directly (root offset -> table -> vtable -> fields), with every
 // offset bounds-checked: the files are untrusted input and nothing may crash or read out of bounds.  Where the
 // reference `unwrap()`s or panics (missing field, no constraints, value wider than 32 bytes) parse() fails with a
-// message instead.  Variable-id translation uses hash maps (first occurrence wins, as `position` does in
-// lib.rs:96-107) instead of the reference's linear scan per matrix entry, which is O(nnz * n).
+// message instead.  Variable-id translation uses a direct table or hash maps (first occurrence wins, as `position` does in
+// lib.rs:96-107) instead of the reference's linear scan per matrix entry, which is O(nnz * n); the constraints are walked
+// by several threads (they are independent tables), the output keeps file order.
 #pragma once
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -54,6 +57,17 @@ class FbView {  // bounds-checked little-endian reads over one buffer
   }
 };
 
+// vector storage that resize() leaves uninitialised: the reader's threads fill every element (350 MB for a 2^20 circuit,
+// whose zero-fill by one thread would cost as much as the parse itself)
+template <typename T>
+struct NoInitAlloc : std::allocator<T> {
+  template <typename U> struct rebind { typedef NoInitAlloc<U> other; };
+  NoInitAlloc() = default;
+  template <typename U> NoInitAlloc(const NoInitAlloc<U>&) {}
+  template <typename U> void construct(U* p) { ::new ((void*)p) U; }
+  template <typename U, typename... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+
 struct ZkVar {
   uint64_t id;
   uint8_t value[32];
@@ -61,8 +75,8 @@ struct ZkVar {
 
 struct ZkR1cs {
   // COO triples in the reference's order (constraint by constraint, a then b then c entries in file order)
-  std::vector<uint64_t> rows[3], cols[3];
-  std::vector<uint8_t> vals[3];
+  std::vector<uint64_t, NoInitAlloc<uint64_t>> rows[3], cols[3];
+  std::vector<uint8_t, NoInitAlloc<uint8_t>> vals[3];
   std::vector<uint8_t> vars, inputs;  // n x 32 canonical bytes
   uint64_t num_cons = 0, num_vars = 0, num_inputs = 0, non_zero_entries = 0;
   uint8_t field_max[32];
@@ -104,7 +118,7 @@ struct ZkR1cs {
     return b.ok;
   }
 
-  bool parse(const uint8_t* cs, size_t cs_len, const uint8_t* hd, size_t hd_len, const uint8_t* wt, size_t wt_len) {
+  bool parse(const uint8_t* cs, size_t cs_len, const uint8_t* hd, size_t hd_len, const uint8_t* wt, size_t wt_len, unsigned threads = 1) {
     FbView bh(hd, hd_len), bc(cs, cs_len), bw(wt, wt_len);
     size_t th = root_message(bh, MSG_HEADER, error, "Circuit Header");
     if (!th) return false;
@@ -122,12 +136,27 @@ struct ZkR1cs {
     if (!variables(bw, bw.field(tw, 0), wit, error)) return false;  // witness.assigned_variables
     num_inputs = in.size();
     num_vars = wit.size();
-    // translate, lib.rs:96-107: witness position, else inputs position + num_vars + 1, else the constant column num_vars
+    // translate, lib.rs:96-107: witness position, else inputs position + num_vars + 1, else the constant column num_vars.
+    // CirC numbers its variables densely, so a direct table serves unless the ids are sparse (then hash maps);
+    // either way the first occurrence of a duplicated id wins, as `position` does.
+    static const uint64_t kNone = ~0ull;
+    uint64_t max_id = 0;
+    for (const ZkVar& v : wit) max_id = std::max(max_id, v.id);
+    for (const ZkVar& v : in) max_id = std::max(max_id, v.id);
+    const bool dense = max_id < 4 * (uint64_t)(wit.size() + in.size()) + 1024;
+    std::vector<uint64_t> table;
     std::unordered_map<uint64_t, uint64_t> wpos, ipos;
-    wpos.reserve(wit.size() * 2);
-    for (size_t i = 0; i < wit.size(); i++) wpos.emplace(wit[i].id, i);  // emplace keeps the first occurrence
-    for (size_t i = 0; i < in.size(); i++) ipos.emplace(in[i].id, i);
+    if (dense) {
+      table.assign(max_id + 1, kNone);
+      for (size_t i = 0; i < wit.size(); i++) if (table[wit[i].id] == kNone) table[wit[i].id] = i;
+      for (size_t i = 0; i < in.size(); i++) if (table[in[i].id] == kNone) table[in[i].id] = i + num_vars + 1;
+    } else {
+      wpos.reserve(wit.size() * 2);
+      for (size_t i = 0; i < wit.size(); i++) wpos.emplace(wit[i].id, i);  // emplace keeps the first occurrence
+      for (size_t i = 0; i < in.size(); i++) ipos.emplace(in[i].id, i);
+    }
     auto translate = [&](uint64_t id) -> uint64_t {
+      if (dense) return id <= max_id && table[id] != kNone ? table[id] : num_vars;
       auto a = wpos.find(id);
       if (a != wpos.end()) return a->second;
       auto c = ipos.find(id);
@@ -138,23 +167,66 @@ struct ZkR1cs {
     if (!fc || !bc.vec(bc.indirect(fc), 4, ncons, cp)) { error = "ConstraintSystem without constraints"; return false; }
     if (ncons == 0) { error = "No constraints given!"; return false; }  // lib.rs:235-237
     num_cons = ncons;
-    uint64_t nz[3] = {0, 0, 0};
-    std::vector<ZkVar> lc;
-    for (size_t i = 0; i < ncons; i++) {
-      size_t t = bc.indirect(cp + 4 * i);
-      if (!bc.ok) { error = "malformed constraint"; return false; }
-      for (unsigned m = 0; m < 3; m++) {
-        if (!variables(bc, bc.field(t, m), lc, error)) return false;
-        for (const ZkVar& v : lc) {
-          rows[m].push_back(i);
-          cols[m].push_back(translate(v.id));
-          vals[m].insert(vals[m].end(), v.value, v.value + 32);
-          bool nonzero = false;
-          for (int k = 0; k < 32; k++) nonzero |= v.value[k] != 0;
-          nz[m] += nonzero;
+    // Constraints are independent tables: slices of them are walked by `threads` threads, first to count the entries of
+    // each matrix (so that every slice knows where its output starts), then to fill.  Output order = file order.
+    const unsigned T = ncons < 4096 || threads < 2 ? 1 : threads;
+    std::vector<uint64_t> cnt(3 * (size_t)T, 0), nzs(3 * (size_t)T, 0);
+    std::vector<std::string> errs(T);
+    auto run = [&](auto&& f) {
+      std::vector<std::thread> th;
+      for (unsigned t = 1; t < T; t++) th.emplace_back([&f, t] { f(t); });
+      f(0);
+      for (auto& x : th) x.join();
+    };
+    run([&](unsigned t) {  // pass 1: number of entries per matrix in this slice (the length of each variable_ids vector)
+      FbView b(cs, cs_len);
+      for (size_t i = ncons * t / T; i < ncons * (t + 1) / T; i++) {
+        size_t tb = b.indirect(cp + 4 * i);
+        if (!b.ok) { errs[t] = "malformed constraint"; return; }
+        for (unsigned m = 0; m < 3; m++) {
+          size_t fp = b.field(tb, m);
+          if (!fp) { errs[t] = "missing Variables table"; return; }
+          size_t vt = b.indirect(fp);
+          size_t fid = b.ok ? b.field(vt, 0) : 0, nid = 0, idp = 0;
+          if (!b.ok || !fid || !b.vec(b.indirect(fid), 8, nid, idp)) { errs[t] = "Variables without variable_ids / values"; return; }
+          cnt[3 * (size_t)t + m] += nid;
         }
       }
+    });
+    for (unsigned t = 0; t < T; t++) if (!errs[t].empty()) { error = errs[t]; return false; }
+    std::vector<uint64_t> start(3 * (size_t)T, 0);
+    for (unsigned m = 0; m < 3; m++) {
+      uint64_t o = 0;
+      for (unsigned t = 0; t < T; t++) { start[3 * (size_t)t + m] = o; o += cnt[3 * (size_t)t + m]; }
+      rows[m].resize(o);
+      cols[m].resize(o);
+      vals[m].resize(32 * o);
     }
+    run([&](unsigned t) {  // pass 2: fill
+      FbView b(cs, cs_len);
+      std::vector<ZkVar> lc;
+      uint64_t at[3] = {start[3 * (size_t)t], start[3 * (size_t)t + 1], start[3 * (size_t)t + 2]};
+      for (size_t i = ncons * t / T; i < ncons * (t + 1) / T; i++) {
+        size_t tb = b.indirect(cp + 4 * i);
+        for (unsigned m = 0; m < 3; m++) {
+          if (!variables(b, b.field(tb, m), lc, errs[t])) return;
+          if (at[m] + lc.size() > start[3 * (size_t)t + m] + cnt[3 * (size_t)t + m]) { errs[t] = "malformed constraint"; return; }
+          for (const ZkVar& v : lc) {
+            rows[m][at[m]] = i;
+            cols[m][at[m]] = translate(v.id);
+            memcpy(&vals[m][32 * at[m]], v.value, 32);
+            bool nonzero = false;
+            for (int k = 0; k < 32; k++) nonzero |= v.value[k] != 0;
+            nzs[3 * (size_t)t + m] += nonzero;
+            at[m]++;
+          }
+        }
+      }
+      if (!b.ok) errs[t] = "malformed flatbuffer";
+    });
+    for (unsigned t = 0; t < T; t++) if (!errs[t].empty()) { error = errs[t]; return false; }
+    uint64_t nz[3] = {0, 0, 0};
+    for (unsigned t = 0; t < T; t++) for (unsigned m = 0; m < 3; m++) nz[m] += nzs[3 * (size_t)t + m];
     non_zero_entries = std::max(nz[0], std::max(nz[1], nz[2]));  // lib.rs:250
     vars.resize(32 * wit.size());
     for (size_t i = 0; i < wit.size(); i++) memcpy(&vars[32 * i], wit[i].value, 32);

@@ -80,69 +80,102 @@ struct CooEntry {
   Fl val;  // Montgomery
 };
 
+// threads for the host-side loops of Instance::new and the zkinterface reader (independent of the prover's worker pool)
+static unsigned ingest_threads(size_t items) {
+  unsigned t = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+  if (g_bound_cpus > 0) t = std::min<unsigned>(t, (unsigned)g_bound_cpus);
+  if (items < (size_t)1 << 15) t = 1;
+  return t;
+}
+template <typename F>
+static void run_threads(unsigned n, F&& f) {  // f(t) for t < n, f(0) on the caller
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < n; t++) th.emplace_back([&f, t] { f(t); });
+  f(0);
+  for (auto& x : th) x.join();
+}
+
+// One (orientation, matrix) of the device form: stable counting sort of the caller's entries by row (CSR) or column (CSC),
+// the op index each position came from (SNARK mode), and the chunk lists of the long segments.  Host only.
+struct SparseHost {
+  std::vector<uint32_t> ptr, idx, op, lseg, lfirst, lo, hi, big;
+  std::vector<Fl> val;
+};
+static void sort_sparse(const std::vector<CooEntry>& M, int orient, uint64_t nseg, uint32_t g, uint32_t k, uint32_t sh, SparseHost& o) {
+  o.ptr.assign(nseg + 1, 0);
+  size_t nnz = 0;
+  for (const CooEntry& e : M) {
+    uint32_t key = orient == 0 ? e.row : e.col;
+    if ((key & (g - 1)) != k) continue;
+    o.ptr[(key >> sh) + 1]++;
+    nnz++;
+  }
+  o.idx.resize(nnz);
+  o.op.resize(g == 1 ? nnz : 0);
+  o.val.resize(nnz);
+  for (uint64_t i = 0; i < nseg; i++) o.ptr[i + 1] += o.ptr[i];
+  std::vector<uint32_t> fill(o.ptr.begin(), o.ptr.end() - 1);
+  uint32_t opi = 0;
+  for (const CooEntry& e : M) {
+    const uint32_t this_op = opi++;
+    uint32_t key = orient == 0 ? e.row : e.col;
+    if ((key & (g - 1)) != k) continue;
+    uint32_t at = fill[key >> sh]++;  // stable: entries of a segment keep the caller's order
+    o.idx[at] = orient == 0 ? e.col : e.row;  // the other coordinate stays global
+    o.val[at] = e.val;
+    if (g == 1) o.op[at] = this_op;
+  }
+  // long segments -> chunk lists (dev.hpp LongSegs)
+  for (uint64_t sgm = 0; sgm < nseg; sgm++) {
+    const uint32_t a = o.ptr[sgm], b = o.ptr[sgm + 1];
+    if (b - a <= sb::kLongSeg) continue;
+    o.lseg.push_back((uint32_t)sgm);
+    o.lfirst.push_back((uint32_t)o.lo.size());
+    for (uint32_t q = a; q < b; q += sb::kSegChunk) { o.lo.push_back(q); o.hi.push_back(std::min(b, q + sb::kSegChunk)); }
+    if (o.lo.size() - o.lfirst.back() > sb::kSumInline) o.big.push_back((uint32_t)o.lseg.size() - 1);
+  }
+  o.lfirst.push_back((uint32_t)o.lo.size());
+}
 static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint64_t ncols, Instance& inst) {
   const uint32_t g = (uint32_t)inst.world, k = (uint32_t)inst.rank, sh = inst.gamma;
+  // the six sorts are independent: one thread each when the matrices are large (0.84 -> 0.2 s for the Otti-shaped 2^20
+  // instance of bench.py); the uploads follow on the calling thread
+  SparseHost H[2][3];
+  const size_t total = M[0].size() + M[1].size() + M[2].size();
+  auto task = [&](unsigned q) { sort_sparse(M[q % 3], (int)(q / 3), (q / 3 == 0 ? nrows : ncols) >> sh, g, k, sh, H[q / 3][q % 3]); };
+  if (ingest_threads(total) >= 6) run_threads(6, task);
+  else if (ingest_threads(total) >= 2) run_threads(2, [&](unsigned t) { for (unsigned q = t; q < 6; q += 2) task(q); });
+  else for (unsigned q = 0; q < 6; q++) task(q);
   for (int orient = 0; orient < 2; orient++) {
     SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
     const uint64_t nseg = (orient == 0 ? nrows : ncols) >> sh;  // segments (rows or columns) this rank owns
     for (int m = 0; m < 3; m++) {
-      std::vector<uint32_t> ptr(nseg + 1, 0);
-      size_t nnz = 0;
-      for (const CooEntry& e : M[m]) {
-        uint32_t key = orient == 0 ? e.row : e.col;
-        if ((key & (g - 1)) != k) continue;
-        ptr[(key >> sh) + 1]++;
-        nnz++;
-      }
-      std::vector<uint32_t> idx(nnz), op(g == 1 ? nnz : 0);
-      std::vector<Fl> val(nnz);
-      for (uint64_t i = 0; i < nseg; i++) ptr[i + 1] += ptr[i];
-      std::vector<uint32_t> fill(ptr.begin(), ptr.end() - 1);
-      uint32_t opi = 0;
-      for (const CooEntry& e : M[m]) {
-        const uint32_t this_op = opi++;
-        uint32_t key = orient == 0 ? e.row : e.col;
-        if ((key & (g - 1)) != k) continue;
-        uint32_t at = fill[key >> sh]++;  // stable: entries of a segment keep the caller's order
-        idx[at] = orient == 0 ? e.col : e.row;  // the other coordinate stays global
-        val[at] = e.val;
-        if (g == 1) op[at] = this_op;
-      }
+      SparseHost& h = H[orient][m];
+      const size_t nnz = h.idx.size();
       if (g == 1) {
         DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
         SB_CUDA(od.alloc(nnz ? nnz : 1));
-        if (nnz) SB_CUDA(cudaMemcpy(od.p, op.data(), nnz * 4, cudaMemcpyHostToDevice));
+        if (nnz) SB_CUDA(cudaMemcpy(od.p, h.op.data(), nnz * 4, cudaMemcpyHostToDevice));
       }
-      {  // long segments -> chunk lists (dev.hpp LongSegs)
-        std::vector<uint32_t> lseg, lfirst, lo, hi, big;
-        for (uint64_t sgm = 0; sgm < nseg; sgm++) {
-          const uint32_t a = ptr[sgm], b = ptr[sgm + 1];
-          if (b - a <= sb::kLongSeg) continue;
-          lseg.push_back((uint32_t)sgm);
-          lfirst.push_back((uint32_t)lo.size());
-          for (uint32_t q = a; q < b; q += sb::kSegChunk) { lo.push_back(q); hi.push_back(std::min(b, q + sb::kSegChunk)); }
-          if (lo.size() - lfirst.back() > sb::kSumInline) big.push_back((uint32_t)lseg.size() - 1);
-        }
-        lfirst.push_back((uint32_t)lo.size());
-        sd.nlong[m] = (uint32_t)lseg.size(); sd.nchunks[m] = (uint32_t)lo.size(); sd.nbig[m] = (uint32_t)big.size();
-        auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
-          cudaError_t e = d.alloc(v.size() ? v.size() : 1);
-          if (e != cudaSuccess || v.empty()) return e;
-          return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
-        };
-        SB_CUDA(put(sd.lg_seg[m], lseg)); SB_CUDA(put(sd.lg_first[m], lfirst)); SB_CUDA(put(sd.lg_lo[m], lo));
-        SB_CUDA(put(sd.lg_hi[m], hi)); SB_CUDA(put(sd.lg_big[m], big));
-        SB_CUDA(sd.lg_partial[m].alloc(lo.size() ? lo.size() : 1));
-        SB_CUDA(sd.lg_reduced[m].alloc(lseg.size() ? lseg.size() : 1));
-      }
+      sd.nlong[m] = (uint32_t)h.lseg.size(); sd.nchunks[m] = (uint32_t)h.lo.size(); sd.nbig[m] = (uint32_t)h.big.size();
+      auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
+        cudaError_t e = d.alloc(v.size() ? v.size() : 1);
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
+      };
+      SB_CUDA(put(sd.lg_seg[m], h.lseg)); SB_CUDA(put(sd.lg_first[m], h.lfirst)); SB_CUDA(put(sd.lg_lo[m], h.lo));
+      SB_CUDA(put(sd.lg_hi[m], h.hi)); SB_CUDA(put(sd.lg_big[m], h.big));
+      SB_CUDA(sd.lg_partial[m].alloc(h.lo.size() ? h.lo.size() : 1));
+      SB_CUDA(sd.lg_reduced[m].alloc(h.lseg.size() ? h.lseg.size() : 1));
       SB_CUDA(sd.ptr[m].alloc(nseg + 1));
       SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
       SB_CUDA(sd.val[m].alloc(nnz ? nnz : 1));
-      SB_CUDA(cudaMemcpy(sd.ptr[m].p, ptr.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
+      SB_CUDA(cudaMemcpy(sd.ptr[m].p, h.ptr.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
       if (nnz) {
-        SB_CUDA(cudaMemcpy(sd.idx[m].p, idx.data(), nnz * 4, cudaMemcpyHostToDevice));
-        SB_CUDA(cudaMemcpy(sd.val[m].p, val.data(), nnz * 32, cudaMemcpyHostToDevice));
+        SB_CUDA(cudaMemcpy(sd.idx[m].p, h.idx.data(), nnz * 4, cudaMemcpyHostToDevice));
+        SB_CUDA(cudaMemcpy(sd.val[m].p, h.val.data(), nnz * 32, cudaMemcpyHostToDevice));
       }
+      h = SparseHost();  // release the host copy
     }
   }
   return SB200_OK;
@@ -219,15 +252,31 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
   std::vector<CooEntry> M[3];
   for (int m = 0; m < 3; m++) {
     if (nnz[m] >= (1ull << 32)) return SB200_ERR_ARG;
-    M[m].reserve(nnz[m]);
-    for (uint64_t k = 0; k < nnz[m]; k++) {
-      uint64_t row = rows[m][k], col = cols[m][k];
-      if (row >= num_cons) { set_error("InvalidIndex: row"); return SB200_ERR_INVALID_INDEX; }                      // lib.rs:166-168
-      if (col >= num_vars + 1 + num_inputs) { set_error("InvalidIndex: col"); return SB200_ERR_INVALID_INDEX; }     // lib.rs:171-173
-      Fl v;
-      if (!fl_from_bytes(vals32[m] + 32 * k, v)) { set_error("InvalidScalar"); return SB200_ERR_INVALID_SCALAR; }   // lib.rs:175-187
-      if (col >= num_vars) col += nvp - num_vars;  // 1 and the inputs live in the second half of z, lib.rs:180-181
-      M[m].push_back(CooEntry{(uint32_t)row, (uint32_t)col, v});
+    M[m].resize(nnz[m]);
+    // entries are checked and converted in slices; the error reported is the one the reference meets first (lowest entry)
+    const unsigned T = ingest_threads(nnz[m]);
+    std::vector<uint64_t> bad_at(T, ~0ull);
+    std::vector<int> bad_code(T, 0);
+    run_threads(T, [&](unsigned t) {
+      const uint64_t k0 = nnz[m] * t / T, k1 = nnz[m] * (t + 1) / T;
+      for (uint64_t k = k0; k < k1; k++) {
+        uint64_t row = rows[m][k], col = cols[m][k];
+        int code = 0;
+        Fl v = fl_zero();
+        if (row >= num_cons) code = 1;                                    // lib.rs:166-168
+        else if (col >= num_vars + 1 + num_inputs) code = 2;              // lib.rs:171-173
+        else if (!fl_from_bytes(vals32[m] + 32 * k, v)) code = 3;         // lib.rs:175-187
+        if (code) { bad_at[t] = k; bad_code[t] = code; return; }
+        if (col >= num_vars) col += nvp - num_vars;  // 1 and the inputs live in the second half of z, lib.rs:180-181
+        M[m][k] = CooEntry{(uint32_t)row, (uint32_t)col, v};
+      }
+    });
+    for (unsigned t = 0; t < T; t++) {
+      if (bad_at[t] == ~0ull) continue;
+      if (bad_code[t] == 1) { set_error("InvalidIndex: row"); return SB200_ERR_INVALID_INDEX; }
+      if (bad_code[t] == 2) { set_error("InvalidIndex: col"); return SB200_ERR_INVALID_INDEX; }
+      set_error("InvalidScalar");
+      return SB200_ERR_INVALID_SCALAR;
     }
     // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product
     // (SNARK::encode would see them as ops: Instance::pad_entries makes sb200_snark_encode refuse such an instance).
@@ -748,7 +797,7 @@ int sb200_zkif_parse(const uint8_t* circuit, size_t circuit_len, const uint8_t* 
   sb200_r1cs* r = new sb200_r1cs();
   bool ok = false;
   try {
-    ok = r->r.parse(circuit, circuit_len, header, header_len, witness, witness_len);
+    ok = r->r.parse(circuit, circuit_len, header, header_len, witness, witness_len, ingest_threads(circuit_len / 64));
   } catch (const std::exception& e) {
     r->r.error = std::string("exception: ") + e.what();
   }

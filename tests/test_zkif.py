@@ -165,6 +165,20 @@ def test_generated_heavy_constant_column_files():
     _same(zkif.R1cs.from_pointers(g.file_ptr(0), g.file_ptr(1), g.file_ptr(2)), spec)
 
 
+def test_threaded_reader_keeps_file_order():
+    """Large constraint systems are walked by several threads (host/zkif.hpp): the triples must come out in file order,
+    exactly the generator's COO lists."""
+    import zkifgen
+    from otti_b200 import zkif
+    g = zkifgen.OttiShaped(30000, 17000, 5, seed=3)
+    r = zkif.R1cs.from_pointers(g.file_ptr(0), g.file_ptr(1), g.file_ptr(2))
+    assert (r.num_cons, r.num_vars, r.num_inputs) == (30000, 17000, 5) and r.nnz == g.nnz
+    for m in range(3):
+        rows, cols, vals = g.coo_arrays(m)
+        assert r.matrix_arrays(m) == (bytes(rows)[:8 * g.nnz[m]], bytes(cols)[:8 * g.nnz[m]], bytes(vals)[:32 * g.nnz[m]])
+    assert bytes(r.vars_assignment().data) == g.vars_bytes()
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("dims", [(1 << 18, 1 << 18, 10), (200000, 1 << 17, 3)])
 def test_prove_otti_shaped_heavy_column_2p18(dims):
