@@ -426,11 +426,32 @@ __global__ void spmvT3_kernel(Csr csc, uint32_t num_cols, const fl_t* __restrict
     uint32_t k0[3], k1[3];
 #pragma unroll
     for (int m = 0; m < 3; m++) { k0[m] = __ldg(csc.ptr[m] + col); k1[m] = __ldg(csc.ptr[m] + col + 1); }
+    // A column's three segments are independent chains of dependent loads (index -> value and gathered e -> product).
+    // Walked one after the other they leave one request in flight per thread; here the first entry of every short
+    // segment is fetched for all three matrices at once (the synthetic shape and most circuit columns have one or two
+    // entries), and only what is left goes through the sequential walk.
+    uint32_t i0[3];
+    fl_t v0[3], e0[3];
+    bool first[3];
+#pragma unroll
+    for (int m = 0; m < 3; m++) {
+      first[m] = k1[m] != k0[m] && k1[m] - k0[m] <= kLongSeg;
+      if (first[m]) { i0[m] = __ldg(csc.idx[m] + k0[m]); v0[m] = ldg_fl(csc.val[m] + k0[m]); }
+    }
+#pragma unroll
+    for (int m = 0; m < 3; m++)
+      if (first[m]) e0[m] = ldg_fl(e + i0[m]);
     fl_t tot = fl_zero();
 #pragma unroll
     for (int m = 0; m < 3; m++) {
       if (k0[m] == k1[m]) continue;
-      const fl_t acc = seg_sum(csc.idx[m], csc.val[m], csc.lg[m], e, col, k0[m], k1[m]);
+      fl_t acc;
+      if (first[m]) {
+        acc = coef_times(v0[m], e0[m]);
+        if (k1[m] - k0[m] > 1) acc = fl_add(acc, seg_sum(csc.idx[m], csc.val[m], csc.lg[m], e, col, k0[m] + 1, k1[m]));
+      } else {
+        acc = seg_sum(csc.idx[m], csc.val[m], csc.lg[m], e, col, k0[m], k1[m]);
+      }
       tot = fl_add(tot, fl_mul_call(m == 0 ? rA : m == 1 ? rB : rC, acc));
     }
     st_fl(out + col, tot);

@@ -79,6 +79,16 @@ struct CooEntry {
   uint32_t row, col;
   Fl val;  // Montgomery
 };
+// vector storage that resize() leaves uninitialised (every element is written by the conversion threads)
+template <typename T>
+struct RawAlloc : std::allocator<T> {
+  template <typename U> struct rebind { typedef RawAlloc<U> other; };
+  RawAlloc() = default;
+  template <typename U> RawAlloc(const RawAlloc<U>&) {}
+  template <typename U> void construct(U* p) { ::new ((void*)p) U; }
+  template <typename U, typename... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
+};
+typedef std::vector<CooEntry, RawAlloc<CooEntry>> CooVec;
 
 // threads for the host-side loops of Instance::new and the zkinterface reader (independent of the prover's worker pool)
 static unsigned ingest_threads(size_t items) {
@@ -101,7 +111,7 @@ struct SparseHost {
   std::vector<uint32_t> ptr, idx, op, lseg, lfirst, lo, hi, big;
   std::vector<Fl> val;
 };
-static void sort_sparse(const std::vector<CooEntry>& M, int orient, uint64_t nseg, uint32_t g, uint32_t k, uint32_t sh, SparseHost& o) {
+static void sort_sparse(const CooVec& M, int orient, uint64_t nseg, uint32_t g, uint32_t k, uint32_t sh, SparseHost& o) {
   o.ptr.assign(nseg + 1, 0);
   size_t nnz = 0;
   for (const CooEntry& e : M) {
@@ -136,48 +146,60 @@ static void sort_sparse(const std::vector<CooEntry>& M, int orient, uint64_t nse
   }
   o.lfirst.push_back((uint32_t)o.lo.size());
 }
-static int upload_sparse(const std::vector<CooEntry> M[3], uint64_t nrows, uint64_t ncols, Instance& inst) {
+static int upload_one(const SparseHost& h, int orient, int m, uint64_t nseg, uint32_t g, Instance& inst) {
+  SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
+  const size_t nnz = h.idx.size();
+  if (g == 1) {
+    DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
+    SB_CUDA(od.alloc(nnz ? nnz : 1));
+    if (nnz) SB_CUDA(cudaMemcpy(od.p, h.op.data(), nnz * 4, cudaMemcpyHostToDevice));
+  }
+  sd.nlong[m] = (uint32_t)h.lseg.size(); sd.nchunks[m] = (uint32_t)h.lo.size(); sd.nbig[m] = (uint32_t)h.big.size();
+  auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
+    cudaError_t e = d.alloc(v.size() ? v.size() : 1);
+    if (e != cudaSuccess || v.empty()) return e;
+    return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
+  };
+  SB_CUDA(put(sd.lg_seg[m], h.lseg)); SB_CUDA(put(sd.lg_first[m], h.lfirst)); SB_CUDA(put(sd.lg_lo[m], h.lo));
+  SB_CUDA(put(sd.lg_hi[m], h.hi)); SB_CUDA(put(sd.lg_big[m], h.big));
+  SB_CUDA(sd.lg_partial[m].alloc(h.lo.size() ? h.lo.size() : 1));
+  SB_CUDA(sd.lg_reduced[m].alloc(h.lseg.size() ? h.lseg.size() : 1));
+  SB_CUDA(sd.ptr[m].alloc(nseg + 1));
+  SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
+  SB_CUDA(sd.val[m].alloc(nnz ? nnz : 1));
+  SB_CUDA(cudaMemcpy(sd.ptr[m].p, h.ptr.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
+  if (nnz) {
+    SB_CUDA(cudaMemcpy(sd.idx[m].p, h.idx.data(), nnz * 4, cudaMemcpyHostToDevice));
+    SB_CUDA(cudaMemcpy(sd.val[m].p, h.val.data(), nnz * 32, cudaMemcpyHostToDevice));
+  }
+  return SB200_OK;
+}
+static int upload_sparse(const CooVec M[3], uint64_t nrows, uint64_t ncols, Instance& inst) {
   const uint32_t g = (uint32_t)inst.world, k = (uint32_t)inst.rank, sh = inst.gamma;
   // the six sorts are independent: one thread each when the matrices are large (0.84 -> 0.2 s for the Otti-shaped 2^20
   // instance of bench.py); the uploads follow on the calling thread
   SparseHost H[2][3];
   const size_t total = M[0].size() + M[1].size() + M[2].size();
-  auto task = [&](unsigned q) { sort_sparse(M[q % 3], (int)(q / 3), (q / 3 == 0 ? nrows : ncols) >> sh, g, k, sh, H[q / 3][q % 3]); };
+  int dev = 0;
+  SB_CUDA(cudaGetDevice(&dev));
+  int rcs[6] = {0, 0, 0, 0, 0, 0};
+  std::string errs[6];
+  // the six (orientation, matrix) pairs are independent: each is sorted and then uploaded by its own thread when the
+  // matrices are large, so that the pageable host->device copies of one overlap the sort of another
+  auto task = [&](unsigned q) {
+    const int orient = (int)(q / 3), m = (int)(q % 3);
+    SparseHost& h = H[orient][m];
+    sort_sparse(M[m], orient, (orient == 0 ? nrows : ncols) >> sh, g, k, sh, h);
+    cudaSetDevice(dev);
+    rcs[q] = upload_one(h, orient, m, (orient == 0 ? nrows : ncols) >> sh, g, inst);
+    if (rcs[q]) errs[q] = get_error();
+    h = SparseHost();  // release the host copy
+  };
   if (ingest_threads(total) >= 6) run_threads(6, task);
   else if (ingest_threads(total) >= 2) run_threads(2, [&](unsigned t) { for (unsigned q = t; q < 6; q += 2) task(q); });
   else for (unsigned q = 0; q < 6; q++) task(q);
-  for (int orient = 0; orient < 2; orient++) {
-    SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
-    const uint64_t nseg = (orient == 0 ? nrows : ncols) >> sh;  // segments (rows or columns) this rank owns
-    for (int m = 0; m < 3; m++) {
-      SparseHost& h = H[orient][m];
-      const size_t nnz = h.idx.size();
-      if (g == 1) {
-        DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
-        SB_CUDA(od.alloc(nnz ? nnz : 1));
-        if (nnz) SB_CUDA(cudaMemcpy(od.p, h.op.data(), nnz * 4, cudaMemcpyHostToDevice));
-      }
-      sd.nlong[m] = (uint32_t)h.lseg.size(); sd.nchunks[m] = (uint32_t)h.lo.size(); sd.nbig[m] = (uint32_t)h.big.size();
-      auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
-        cudaError_t e = d.alloc(v.size() ? v.size() : 1);
-        if (e != cudaSuccess || v.empty()) return e;
-        return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
-      };
-      SB_CUDA(put(sd.lg_seg[m], h.lseg)); SB_CUDA(put(sd.lg_first[m], h.lfirst)); SB_CUDA(put(sd.lg_lo[m], h.lo));
-      SB_CUDA(put(sd.lg_hi[m], h.hi)); SB_CUDA(put(sd.lg_big[m], h.big));
-      SB_CUDA(sd.lg_partial[m].alloc(h.lo.size() ? h.lo.size() : 1));
-      SB_CUDA(sd.lg_reduced[m].alloc(h.lseg.size() ? h.lseg.size() : 1));
-      SB_CUDA(sd.ptr[m].alloc(nseg + 1));
-      SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
-      SB_CUDA(sd.val[m].alloc(nnz ? nnz : 1));
-      SB_CUDA(cudaMemcpy(sd.ptr[m].p, h.ptr.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
-      if (nnz) {
-        SB_CUDA(cudaMemcpy(sd.idx[m].p, h.idx.data(), nnz * 4, cudaMemcpyHostToDevice));
-        SB_CUDA(cudaMemcpy(sd.val[m].p, h.val.data(), nnz * 32, cudaMemcpyHostToDevice));
-      }
-      h = SparseHost();  // release the host copy
-    }
-  }
+  for (int q = 0; q < 6; q++)
+    if (rcs[q]) { set_error(errs[q]); return rcs[q]; }
   return SB200_OK;
 }
 // world must be 1, 2, 4 or 8 and leave every rank at least two constraint rows, two z columns and one commitment row
@@ -249,7 +271,15 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
     set_error("instance too large for 32-bit indices");
     return SB200_ERR_ARG;
   }
-  std::vector<CooEntry> M[3];
+  const bool itrace = getenv("SB200_TRACE_INSTANCE") != nullptr;  // stage times of this call on stderr
+  double it0 = now_s();
+  auto imark = [&](const char* what) {
+    if (!itrace) return;
+    double t = now_s();
+    fprintf(stderr, "[sb200-instance] %8.3f ms  %s\n", (t - it0) * 1e3, what);
+    it0 = t;
+  };
+  CooVec M[3];
   for (int m = 0; m < 3; m++) {
     if (nnz[m] >= (1ull << 32)) return SB200_ERR_ARG;
     M[m].resize(nnz[m]);
@@ -281,6 +311,7 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
     // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product
     // (SNARK::encode would see them as ops: Instance::pad_entries makes sb200_snark_encode refuse such an instance).
   }
+  imark("entries checked and converted");
   uint32_t gamma = 0;
   int rc = shard_check(rank, world, ncp, nvp, gamma);
   if (rc) return rc;
@@ -293,6 +324,7 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
   inst->pad_entries = num_cons == 0 || num_cons == 1;
   rc = upload_sparse(M, ncp, 2 * nvp, *inst);
   if (rc) { delete inst; return rc; }
+  imark("CSR / CSC sorted and uploaded");
   *out = reinterpret_cast<sb200_instance*>(inst);
   return SB200_OK;
 }
@@ -350,7 +382,7 @@ int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint6
     Zinv[i] = fl_mul(acc, pre[i]);
     acc = fl_mul(acc, Z[i]);
   }
-  std::vector<CooEntry> M[3];
+  CooVec M[3];
   for (int m = 0; m < 3; m++) M[m].reserve(num_cons);
   for (uint64_t i = 0; i < num_cons; i++) {
     uint64_t ai = i % size_z, bi = (i + 2) % size_z, ci = (i + 3) % size_z;

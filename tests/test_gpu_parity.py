@@ -310,6 +310,41 @@ def test_generators_and_commit_rows(sb, nv):
     assert bytes(c) == O.pt_msm(mont([xs[-1], blinds[-1]]), og.point(2) + og.point(1))
 
 
+@pytest.mark.parametrize("c", [2, 5, 8, 11, 13, 16])
+def test_commit_rows_short_scalars_every_window_width(sb, c):
+    """The commitment kernel stops a short scalar after (bitlen - 1) / c + 2 windows (the recoding carry can reach one
+    window above the top bit).  Scalars 2^k - 1, 2^k, 2^k + 1 for k around the multiples of c, all-ones words and
+    bits, under window widths where (bitlen - 1) / c sits on a window boundary: a dropped carry would change a row."""
+    nv = 256
+    old = os.environ.get("SB200_MSM_WINDOW")
+    os.environ["SB200_MSM_WINDOW"] = str(c)
+    try:
+        pg = sb.NIZKGens.new(nv, nv, 1)
+    finally:
+        if old is None:
+            os.environ.pop("SB200_MSM_WINDOW", None)
+        else:
+            os.environ["SB200_MSM_WINDOW"] = old
+    assert pg.window_bits == c
+    og = O.Gens(nv, nv, 1)
+    xs = []
+    for m in range(1, 10):
+        k = m * c
+        for kk in (k - 1, k, k + 1):
+            for dv in (-1, 0, 1):
+                v = (1 << kk) + dv
+                if 0 <= v < ELL:
+                    xs.append(v)
+    xs += [0, 1, 2**32 - 1, 2**64 - 1, 2**16 - 1, 2**15, 2**15 + 1, 2**251, 2**252, ELL - 1, ELL - 2]
+    rng = rand_scalars(nv, 97)
+    xs = (xs + rng)[:nv]
+    Ls = 1 << ((nv.bit_length() - 1) // 2)
+    blinds = rand_scalars(Ls, 98)
+    o = _out(32 * Ls)
+    assert sb.lib().sb200_k_commit_rows(pg.h, _buf(canon(xs)), C.c_size_t(nv), _buf(canon(blinds)), C.c_size_t(Ls), o) == 0
+    assert bytes(o) == og.commit_rows(mont(xs), mont(blinds))
+
+
 def test_merlin(sb):
     o = _out(32)
     sb.lib().sb200_k_merlin(_buf(b"test protocol"), C.c_size_t(13), b"some label", _buf(b"some data"), C.c_size_t(9),
