@@ -180,26 +180,19 @@ static int upload_sparse(const CooVec M[3], uint64_t nrows, uint64_t ncols, Inst
   // instance of bench.py); the uploads follow on the calling thread
   SparseHost H[2][3];
   const size_t total = M[0].size() + M[1].size() + M[2].size();
-  int dev = 0;
-  SB_CUDA(cudaGetDevice(&dev));
-  int rcs[6] = {0, 0, 0, 0, 0, 0};
-  std::string errs[6];
-  // the six (orientation, matrix) pairs are independent: each is sorted and then uploaded by its own thread when the
-  // matrices are large, so that the pageable host->device copies of one overlap the sort of another
-  auto task = [&](unsigned q) {
-    const int orient = (int)(q / 3), m = (int)(q % 3);
-    SparseHost& h = H[orient][m];
-    sort_sparse(M[m], orient, (orient == 0 ? nrows : ncols) >> sh, g, k, sh, h);
-    cudaSetDevice(dev);
-    rcs[q] = upload_one(h, orient, m, (orient == 0 ? nrows : ncols) >> sh, g, inst);
-    if (rcs[q]) errs[q] = get_error();
-    h = SparseHost();  // release the host copy
-  };
+  // the six (orientation, matrix) sorts are independent: one thread each when the matrices are large; the uploads then
+  // follow on the calling thread (pageable copies issued from several threads at once serialise in the driver and came
+  // out 2x slower than this on the Otti-shaped 2^20 instance)
+  auto task = [&](unsigned q) { sort_sparse(M[q % 3], (int)(q / 3), (q / 3 == 0 ? nrows : ncols) >> sh, g, k, sh, H[q / 3][q % 3]); };
   if (ingest_threads(total) >= 6) run_threads(6, task);
   else if (ingest_threads(total) >= 2) run_threads(2, [&](unsigned t) { for (unsigned q = t; q < 6; q += 2) task(q); });
   else for (unsigned q = 0; q < 6; q++) task(q);
-  for (int q = 0; q < 6; q++)
-    if (rcs[q]) { set_error(errs[q]); return rcs[q]; }
+  for (unsigned q = 0; q < 6; q++) {
+    const int orient = (int)(q / 3), m = (int)(q % 3);
+    int rc = upload_one(H[orient][m], orient, m, (orient == 0 ? nrows : ncols) >> sh, g, inst);
+    if (rc) return rc;
+    H[orient][m] = SparseHost();  // release the host copy
+  }
   return SB200_OK;
 }
 // world must be 1, 2, 4 or 8 and leave every rank at least two constraint rows, two z columns and one commitment row
