@@ -262,7 +262,7 @@ def kernel_profile(sb, run, reps=2):
 
 def int_pipe_peak(sm_mhz):
     """IMAD.WIDE.U32 issue rate of the whole chip.  One warp instruction per 4 cycles per SM sub-partition = 8 lanes per
-    clock per sub-partition: measured with tools/microbench/fpmul_bench under ncu (profiles/r02_fpmul_pipe.txt)."""
+    clock per sub-partition: measured with tools/microbench/fpmul_bench under ncu (profiles/r02a_pipe_fpmul.csv + r02a_pipe_msm_fixed_2p22.csv)."""
     return 148 * 4 * 8 * sm_mhz * 1e6
 
 
@@ -292,7 +292,7 @@ def roofline_for(kernel, kernel_s, share, s, c, sm_mhz, extra=None):
             "achieved": imad / kernel_s / 1e9 if kernel_s > 0 else 0.0, "peak": peak / 1e9, "unit": "GIMAD/s (IMAD.WIDE.U32 lane-operations)",
             "frac": (imad / kernel_s) / peak if kernel_s > 0 else 0.0,
             "peak_source": "148 SM x 4 sub-partitions x 8 lanes/clk x %.0f MHz (sampled under load); 1 IMAD.WIDE.U32 warp instruction "
-                           "per 4 cycles per sub-partition, profiles/r02_fpmul_pipe.txt" % sm_mhz,
+                           "per 4 cycles per sub-partition, profiles/r02a_pipe_fpmul.csv + r02a_pipe_msm_fixed_2p22.csv" % sm_mhz,
             "algorithmic_imad": imad, "algorithmic_bytes": alg_bytes,
             "hbm": {"bound": "hbm", "achieved": alg_bytes / kernel_s / 1e9 if kernel_s > 0 else 0.0, "peak": hbm_peak, "unit": "GB/s",
                     "frac": alg_bytes / kernel_s / 1e9 / hbm_peak if kernel_s > 0 else 0.0, "peak_source": which},

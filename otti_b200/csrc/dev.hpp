@@ -181,7 +181,20 @@ struct PcBatch {
 // One round of SumcheckInstanceProof::prove_cubic_batched (sumcheck.rs:252-422) on tables of length n_old: if do_bind
 // every table is first bound at r (-> n_old / 2); then the round's combined evaluations at 0, 2, 3 go to w.result and
 // the mailbox.  Lengths are powers of two, length after the bind >= 2.
-cudaError_t k_pc_round(const PcBatch& b, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s);
+// Doorbell: a round kernel can be launched AHEAD of its challenge (while the host still works on the previous round) and
+// then waits, on the device, until the host has stored r into *r and `want` into *flag (both in mapped pinned host
+// memory).  That takes the launch latency out of the round trip: ~9.5 -> ~4.5 us of fixed cost per Fiat-Shamir round
+// (tools/microbench/roundtrip_bench.cu).  flag == NULL: r comes as a launch argument as before.  A kernel whose bell is
+// never rung gives up after ~2 s without touching the tables or the mailbox.
+struct Bell {
+  const uint32_t* flag = nullptr;  // mapped host memory: the doorbell
+  const fl_t* r = nullptr;         // mapped host memory: the challenge
+  uint32_t* relay = nullptr;       // device memory, 16 words: only block 0 polls the host (a grid of blocks polling over
+                                   // PCIe starves the very writes it waits for); it passes flag and r on through here
+  uint32_t want = 0;
+};
+cudaError_t k_pc_round(const PcBatch& b, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s,
+                       const Bell* bell = nullptr);
 // host_out[3k + t] = final value of table t (A, B, own C / zero) of instance k, after a last bind at r if do_bind
 cudaError_t k_pc_final(const PcBatch& b, bool do_bind, fl_t r, fl_t* host_out, uint32_t* host_flag, uint32_t seq, cudaStream_t s);
 // out[j] = sum_i X_j[i] * Y_j[i] (* W_j[i] if W_j != NULL), j < nvec; tmp: multi_dot_tmp_scalars(nvec).

@@ -77,6 +77,7 @@ struct Workspace {  // sized by (num_cons, num_vars); allocated on first prove
   DevBuf<sb::fl_t> vars_canon, varsM, z, zloc, abc, T, A, B, C, eq_tmp, sc_partials, small, blinds, bound_tmp, LZ, bl_a, bl_b,
       coeff0, coeff1, srows;
   DevBuf<unsigned int> counter;
+  DevBuf<uint32_t> bell_relay;  // 16 words: flag + challenge passed on by block 0 of a kernel waiting for a doorbell (dev.hpp Bell)
   DevBuf<uint32_t> flag;
   DevBuf<uint8_t> msm_scratch, pts;
   uint8_t* pinned = nullptr;  // host staging
