@@ -31,6 +31,7 @@ static thread_local double g_profile[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 
 static std::atomic<uint64_t> g_h2d_bytes{0}, g_d2h_bytes{0};  // one proof at a time per process (prove_mu); counted from two threads
 
 static bool g_device_ok = false;
+static thread_local int g_window_override = 0;  // set around sb200_gens_new_for by sb200_snark_gens_new_for (snark.inc)
 static int g_bound_cpus = 0;
 static int ensure_device() {
   if (g_device_ok) return SB200_OK;
@@ -592,6 +593,7 @@ int sb200_gens_new_for(const uint8_t* label, size_t label_len, uint64_t num_cons
       if (best == 0 || cost < best) { best = cost; c = cc; }
     }
   }
+  if (g_window_override >= 2 && g_window_override <= 16) c = (uint32_t)g_window_override;  // SNARKGens: widths chosen jointly
   if (const char* env = getenv("SB200_MSM_WINDOW")) {
     int v = atoi(env);
     if (v >= 2 && v <= 16) c = (uint32_t)v;

@@ -67,6 +67,40 @@ def test_closed_form_lengths_match_the_reference_profile():
     assert len_r1cs_eval_proof(n, n, n) == 133720
 
 
+def _golden():
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "snark_prove_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("case", _golden()["cases"], ids=lambda c: "%dx%d" % (c["num_cons"], c["num_vars"]))
+def test_oracle_snark_matches_committed_digests(case):
+    """tests/golden/snark_prove_golden.json (made by tests/golden/make_snark_prove_golden.py): the oracle's proof bytes for
+    fixed seeds, so that the checker itself cannot drift unnoticed."""
+    import hashlib
+    inst, v, i = O.Instance.synthetic(case["num_cons"], case["num_vars"], case["num_inputs"], case["seed"])
+    assert max(inst.nnz) == case["num_nz_entries"]
+    pf = O.snark_prove(inst, case["num_nz_entries"], v, i, LABEL, TAPE_SEED)
+    assert len(pf) == case["proof_len"] and pf[:64].hex() == case["proof_head"] and pf[-64:].hex() == case["proof_tail"]
+    assert hashlib.sha256(pf).hexdigest() == case["proof_sha256"]
+    assert hashlib.sha256(O.snark_encode(inst, case["num_nz_entries"])).hexdigest() == case["commitment_sha256"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", _golden()["cases"], ids=lambda c: "%dx%d" % (c["num_cons"], c["num_vars"]))
+def test_gpu_snark_matches_committed_digests(case):
+    """The CUDA path against the committed digests directly (no oracle call in the loop)."""
+    import hashlib
+    import otti_b200 as sb
+    inst, vars_, inputs = sb.Instance.produce_synthetic_r1cs(case["num_cons"], case["num_vars"], case["num_inputs"], case["seed"])
+    gens = sb.SNARKGens.new(case["num_cons"], case["num_vars"], case["num_inputs"], case["num_nz_entries"])
+    comm = sb.SNARK.encode(inst, gens)
+    assert hashlib.sha256(comm.to_bytes()).hexdigest() == case["commitment_sha256"]
+    pf = sb.SNARK.prove(inst, comm, None, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE_SEED).to_bytes()
+    assert len(pf) == case["proof_len"] and hashlib.sha256(pf).hexdigest() == case["proof_sha256"]
+
+
 SIZES = [(8, 8, 2), (16, 8, 3), (32, 64, 10), (64, 64, 10), (256, 256, 10)]
 
 
