@@ -615,8 +615,9 @@ __global__ void __launch_bounds__(256) sc_cubic_lat_kernel(fl_t* __restrict__ T,
   fl_t* X = k == 0 ? T : k == 1 ? A : k == 2 ? B : C;
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 4) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
   fl_t e = fl_zero();
-  // 64 pairs per block and pass; the pass count is the same for every thread of a block (barriers inside)
-  for (size_t base = (size_t)blockIdx.x * 64; base < h; base += (size_t)gridDim.x * 64) {
+  // blockDim / 4 pairs per block and pass; the pass count is the same for every thread of a block (barriers inside)
+  const size_t upb = blockDim.x >> 2;
+  for (size_t base = (size_t)blockIdx.x * upb; base < h; base += (size_t)gridDim.x * upb) {
     const size_t pair = base + pl;
     fl_t lo = fl_zero(), hi = fl_zero();
     if (pair < h) {
@@ -632,7 +633,7 @@ __global__ void __launch_bounds__(256) sc_cubic_lat_kernel(fl_t* __restrict__ T,
       }
     }
     const fl_t d = fl_sub(hi, lo), p2 = fl_add(hi, d), p3 = fl_add(p2, d);  // values at 0, 2, 3 of this table's line
-    if (base != (size_t)blockIdx.x * 64) __syncthreads();  // the previous pass has read sv
+    if (base != (size_t)blockIdx.x * upb) __syncthreads();  // the previous pass has read sv
     sv[pl][0][k] = lo;
     sv[pl][1][k] = p2;
     sv[pl][2][k] = p3;
@@ -652,7 +653,8 @@ __global__ void __launch_bounds__(256) sc_quad_lat_kernel(fl_t* __restrict__ Z, 
   fl_t* X = (k & 1) ? Q : Z;
   if (BIND && newlen == 1 && blockIdx.x == 0 && threadIdx.x < 2) st_fl(X, bind1<FlInl>(ld_fl(X), ld_fl(X + 1), r));
   fl_t e = fl_zero();
-  for (size_t base = (size_t)blockIdx.x * 64; base < h; base += (size_t)gridDim.x * 64) {
+  const size_t upb = blockDim.x >> 2;
+  for (size_t base = (size_t)blockIdx.x * upb; base < h; base += (size_t)gridDim.x * upb) {
     const size_t pair = base + pl;
     const size_t at = pair + ((k & 2) ? h : 0);
     fl_t v = fl_zero();
@@ -664,7 +666,7 @@ __global__ void __launch_bounds__(256) sc_quad_lat_kernel(fl_t* __restrict__ Z, 
         v = ld_fl(X + at);
       }
     }
-    if (base != (size_t)blockIdx.x * 64) __syncthreads();  // the previous pass has read sv
+    if (base != (size_t)blockIdx.x * upb) __syncthreads();  // the previous pass has read sv
     sv[pl][k] = v;
     __syncthreads();
     if (pair < h) {  // sumcheck.rs:459-467
@@ -682,8 +684,20 @@ static size_t lat_pairs_setting() {  // SB200_SC_LAT_PAIRS: experiment knob (the
   }();
   return v;
 }
+// Threads per block of the four-lanes-per-pair kernels.  128 = one warp per SM sub-partition: a dependent F_l product costs
+// a warp about half as much when it does not share the sub-partition's integer pipe (tools/microbench/roundtrip_bench.cu).
+// SB200_LAT_THREADS overrides (256 = the shape before).
+static unsigned lat_threads() {
+  static const unsigned v = [] {
+    const char* e = getenv("SB200_LAT_THREADS");
+    int t = e ? atoi(e) : 128;
+    return (unsigned)(t == 64 || t == 128 || t == 256 ? t : 128);
+  }();
+  return v;
+}
 static inline unsigned lat_grid(size_t pairs, const ScWork& w) {
-  size_t g = (pairs + 63) / 64, cap = ((size_t)w.max_blocks * 3) / 4;  // the partials buffer holds max_blocks * 3 scalars, four per block here
+  const size_t upb = lat_threads() / 4;
+  size_t g = (pairs + upb - 1) / upb, cap = ((size_t)w.max_blocks * 3) / 4;  // the partials buffer holds max_blocks * 3 scalars, four per block here
   if (const char* e = getenv("SB200_SC_LAT_BLOCKS")) cap = std::min<size_t>(cap, (size_t)atoi(e));
   return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
 }
@@ -701,8 +715,8 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   Mailbox mb{w.host_result, w.host_flag, w.seq};
   if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
     unsigned gl = lat_grid(newlen / 2, w);
-    if (do_bind) { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<true><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
-    else { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<false><<<gl, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+    if (do_bind) { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<true><<<gl, lat_threads(), 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+    else { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<false><<<gl, lat_threads(), 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
   const bool compact = g <= kCompactBlocks;
@@ -718,8 +732,8 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
   Mailbox mb{w.host_result, w.host_flag, w.seq};
   if (newlen / 2 <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64) {
     unsigned gl = lat_grid(newlen / 2, w);
-    if (do_bind) { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<true><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
-    else { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<false><<<gl, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+    if (do_bind) { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<true><<<gl, lat_threads(), 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
+    else { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<false><<<gl, lat_threads(), 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
   const bool compact = g <= kCompactBlocks;
@@ -1498,9 +1512,22 @@ __global__ void __launch_bounds__(256) msm_small_kernel(const niels_t* __restric
     }
   }
 }
+// Threads per block of the small MSM.  One warp per SM sub-partition: a dependent F_p product costs a warp 0.23 us when
+// it has the sub-partition's integer pipe to itself and 0.50 us when two warps share it (tools/microbench/roundtrip_bench.cu:
+// 16 dependent products in a 32-thread block against a 256-thread block), and this kernel is a tree of dependent
+// additions.  SB200_MSM_SMALL_THREADS overrides (256 = the shape before).
+static uint32_t msm_small_threads() {
+  static const uint32_t v = [] {
+    const char* e = getenv("SB200_MSM_SMALL_THREADS");
+    int t = e ? atoi(e) : 128;
+    return (uint32_t)(t == 32 || t == 64 || t == 128 || t == 256 ? t : 128);
+  }();
+  return v;
+}
 uint32_t msm_small_blocks(uint32_t rows, uint32_t n, uint32_t windows) {
   uint32_t pairs = n * windows;
-  uint32_t want = (pairs + 511) / 512;  // ~2 look-ups per thread
+  const uint32_t per_block = 2 * msm_small_threads();
+  uint32_t want = (pairs + per_block - 1) / per_block;  // ~2 look-ups per thread
   uint32_t cap = (uint32_t)(kSMs * 2) / (rows ? rows : 1);
   if (cap < 1) cap = 1;
   if (want < 1) want = 1;
@@ -1513,7 +1540,7 @@ cudaError_t msm_small(const MsmTable& t, const fl_t* scalars, size_t stride, uin
                       unsigned int* counters, void* out_ext, uint32_t* host_flag, uint32_t seq, cudaStream_t s) {
   if (!rows) return cudaSuccess;
   dim3 grid(msm_small_blocks(rows, n, t.windows), rows);
-  { KProf kp_("msm_small_kernel", s); msm_small_kernel<<<grid, 256, 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, reinterpret_cast<ge_t*>(scratch), counters,
+  { KProf kp_("msm_small_kernel", s); msm_small_kernel<<<grid, msm_small_threads(), 0, s>>>(t.tbl, t.c, t.windows, scalars, stride, n, reinterpret_cast<ge_t*>(scratch), counters,
                                         reinterpret_cast<ge_t*>(out_ext), host_flag, seq); }
   return SB_LAUNCHED();
 }
