@@ -69,14 +69,14 @@ class HostPool {
   }
 
  public:
-  // Each worker on a core of its own (the k-th CPU of the set this process may use, the first left to the posting
-  // thread).  Unpinned, the scheduler moves the spinning workers around between proofs and a 2^16 proof comes out
-  // bimodal from process to process (2.07 or 2.25 ms).  SB200_PIN_WORKERS=0 leaves the threads where the OS puts them.
+  // SB200_PIN_WORKERS=1: each worker on a core of its own (the k-th CPU of the set this process may use, the first left
+  // to the posting thread).  Off by default: a 2^16 proof comes out at 2.06 - 2.30 ms from process to process either way
+  // (three alternating runs each on a B200 box), so the spread is not the scheduler moving the workers.
   explicit HostPool(int n) {
     std::vector<int> cpus;
 #if defined(__linux__)
     const char* pe = getenv("SB200_PIN_WORKERS");
-    if (!(pe && atoi(pe) == 0)) {
+    if (pe && atoi(pe) != 0) {
       cpu_set_t cur;
       CPU_ZERO(&cur);
       if (sched_getaffinity(0, sizeof cur, &cur) == 0)
