@@ -31,6 +31,7 @@ static thread_local double g_profile[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 
 static std::atomic<uint64_t> g_h2d_bytes{0}, g_d2h_bytes{0};  // one proof at a time per process (prove_mu); counted from two threads
 
 static bool g_device_ok = false;
+static std::mutex g_prove_mu;  // NIZK::prove and SNARK::prove: one proof at a time per process (the worker pool has a single posting thread)
 static thread_local int g_window_override = 0;  // set around sb200_gens_new_for by sb200_snark_gens_new_for (snark.inc)
 static int g_bound_cpus = 0;
 static int ensure_device() {
@@ -770,8 +771,7 @@ int sb200_nizk_prove(const sb200_instance* hi, const uint8_t* vars32, uint64_t n
   }
   Fl seed_scalar = fl_from_bytes_wide(seed);
   NizkProof pf;
-  static std::mutex prove_mu;  // one proof at a time per process: the host worker pool has a single posting thread
-  std::lock_guard<std::mutex> prove_lock(prove_mu);
+  std::lock_guard<std::mutex> prove_lock(g_prove_mu);  // one proof at a time per process: the host worker pool has a single posting thread
   try {
     if (transcript) {
       VtTranscript tr(transcript);
