@@ -282,6 +282,24 @@ static inline Ge ge_scalarmul(const Fl& k, const Ge& p) {
   return ge_scalarmul(kb, p);
 }
 
+// a*P + b*Q with one shared doubling chain (Straus, 4-bit windows): the verifier's comm_target = w0*C1 + w1*C2
+static inline Ge ge_double_scalarmul(const Fl& a, const Ge& p, const Fl& b, const Ge& q) {
+  uint8_t ka[32], kb[32];
+  fl_to_bytes(a, ka);
+  fl_to_bytes(b, kb);
+  Ge tp[16], tq[16];
+  tp[0] = tq[0] = ge_identity();
+  for (int i = 1; i < 16; i++) { tp[i] = ge_add(tp[i - 1], p); tq[i] = ge_add(tq[i - 1], q); }
+  Ge acc = ge_identity();
+  for (int i = 63; i >= 0; i--) {
+    for (int j = 0; j < 4; j++) acc = ge_double(acc);
+    const int da = (ka[i >> 1] >> ((i & 1) * 4)) & 15, db = (kb[i >> 1] >> ((i & 1) * 4)) & 15;
+    if (da) acc = ge_add(acc, tp[da]);
+    if (db) acc = ge_add(acc, tq[db]);
+  }
+  return acc;
+}
+
 // Batch-normalise extended points to affine Niels with one inversion.
 static inline void ge_batch_to_niels(const Ge* pts, size_t n, GeNiels* out) {
   if (!n) return;
