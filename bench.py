@@ -446,6 +446,60 @@ def side_otti(env, s):
     return out
 
 
+def side_otti_sweep(env, sizes=(12, 14, 16, 18)):
+    """The Otti suites span 2^12 .. 2^20 constraints (SURVEY.md section 8(d) ii): the same Otti-shaped generator at the smaller
+    sizes, compact records -- one-shot path (parse, Instance::new, generators for one proof, prove, verify) and steady prove /
+    verify -- with the CPU restatement's prove beside them."""
+    sb, torch = env.sb, env.torch
+    import statistics
+    import zkifgen
+    from otti_b200 import zkif
+    out = []
+    for s in sizes:
+        n = 1 << s
+        g = zkifgen.OttiShaped(n, n, NUM_INPUTS, seed=11)
+        t0 = time.perf_counter()
+        r = zkif.R1cs.from_pointers(g.file_ptr(0), g.file_ptr(1), g.file_ptr(2))
+        inst = r.instance()
+        vars_, inputs = r.vars_assignment(), r.inputs_assignment()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        gens = r.nizk_public_params(proofs_expected=1)
+        proof = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE)
+        t2 = time.perf_counter()
+        proof.verify(inst, inputs, sb.Transcript.new(LABEL), gens)
+        t3 = time.perf_counter()
+        del gens
+        gens = r.nizk_public_params()
+        for _ in range(2):
+            sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE)
+        tp, tv = [], []
+        for _ in range(7):
+            ta = time.perf_counter()
+            p2 = sb.NIZK.prove(inst, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE)
+            tp.append(1e3 * (time.perf_counter() - ta))
+            ta = time.perf_counter()
+            p2.verify(inst, inputs, sb.Transcript.new(LABEL), gens)
+            tv.append(1e3 * (time.perf_counter() - ta))
+        rec = {"log_size": s, "nnz": sum(g.nnz), "one_shot": {"ingest_s": round(t1 - t0, 4), "gens_plus_prove_s": round(t2 - t1, 4),
+                                                               "verify_s": round(t3 - t2, 4), "total_s": round(t3 - t0, 4)},
+               "steady_prove_ms": round(statistics.median(tp), 3), "steady_verify_ms": round(statistics.median(tv), 3),
+               "proof_bytes": len(proof.to_bytes()), "proof_same_with_both_generator_tables": p2.to_bytes() == proof.to_bytes()}
+        if not env.args.no_cpu_baseline:
+            import oracle_lib as O
+            oi = O.Instance.new_arrays(n, n, NUM_INPUTS, [g.coo_arrays(m) + (g.nnz[m],) for m in range(3)])
+            og = O.Gens(n, n, NUM_INPUTS)
+            threads = host_threads()
+            ta = time.perf_counter()
+            want = O.nizk_prove(oi, g.vars_bytes(), g.inputs_bytes(), og, LABEL, TAPE, threads)
+            rec["cpu_port_prove_s"] = round(time.perf_counter() - ta, 4)
+            rec["cpu_port_cores"] = threads
+            rec["proof_bytes_equal_cpu_port"] = want == proof.to_bytes()
+        out.append(rec)
+        del gens, inst
+    return out
+
+
 def snark_side_measurements(sb, inst, n, s):
     """SNARK mode on a 2^16 instance, outside the timed region of the headline metric: whole-call
     milliseconds (best of 4) of each step, then SNARK::prove / verify.  Never fails the bench line."""
@@ -774,6 +828,10 @@ def main():
             side["otti_shaped"] = side_otti(env, args.otti_log_size)
         except Exception as e:
             side["otti_shaped"] = {"error": "%s: %s" % (type(e).__name__, e)}
+        try:
+            side["otti_shaped_sweep"] = side_otti_sweep(env)
+        except Exception as e:
+            side["otti_shaped_sweep"] = {"error": "%s: %s" % (type(e).__name__, e)}
         line["side"] = side
     if per_rank is not None:
         line["per_rank"] = per_rank

@@ -874,9 +874,15 @@ def zk_sumcheck_verify(pf, comm_claim, num_rounds, degree, g1, gn, tr):
 # NIZK::prove / verify (lib.rs:493-574, r1csproof.rs:141-498)
 # ----------------------------------------------------------------------------
 def nizk_prove(inst, vars_, inputs, gens, tr, tape_seed):
+    """NIZK::prove, lib.rs:493-535."""
     tape = RandomTape(b"proof", tape_seed)
     tr.append_protocol_name(b"Spartan NIZK proof")
     vars_ = list(vars_) + [0] * (inst.num_vars - len(vars_))
+    return r1cs_prove(inst, vars_, inputs, gens, tr, tape)
+
+
+def r1cs_prove(inst, vars_, inputs, gens, tr, tape):
+    """R1CSProof::prove, r1csproof.rs:141-345 (shared by NIZK::prove and SNARK::prove; vars_ already padded)."""
     tr.append_protocol_name(b"R1CS proof")
     assert len(inputs) < len(vars_)
     nv = len(vars_)
