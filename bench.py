@@ -60,7 +60,8 @@ def parse_args():
     ap.add_argument("--otti-log-size", type=int, default=20, help="log2 constraints of the Otti-shaped side entry")
     ap.add_argument("--shard-log-sizes", default="22,24",
                     help="N > 1: log2 sizes of the ONE proof additionally sharded over all N GPUs (configs[4]); empty = skip")
-    ap.add_argument("--exchange", default="shm", choices=["shm", "nccl"], help="exchange hook of the sharded proof")
+    ap.add_argument("--exchange", default="shm", choices=["shm", "nccl", "nccl-native"],
+                    help="exchange hook of the sharded proof: POSIX shared memory, torch.distributed (NCCL through a Python callback), ncclAllGather called natively")
     return ap.parse_args()
 
 
@@ -612,7 +613,8 @@ def run_sharded(env, s):
     n = 1 << s
     name = ["/sb200-bench-" + uuid.uuid4().hex[:12]]
     dist.broadcast_object_list(name, src=0)
-    comm = sbcomm.ShmComm(name[0], rank, world) if args.exchange == "shm" else sbcomm.DistComm()
+    comm = (sbcomm.ShmComm(name[0], rank, world) if args.exchange == "shm" else
+            sbcomm.NcclNativeComm() if args.exchange == "nccl-native" else sbcomm.DistComm())
     inst, vars_, inputs = sb.Instance.produce_synthetic_r1cs(n, n, NUM_INPUTS, SEED, pinned=True, rank=rank, world=world)
     gens = sb.NIZKGens.new(n, n, NUM_INPUTS)
     proof = None

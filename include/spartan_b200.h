@@ -109,6 +109,12 @@ typedef struct sb200_comm_vt {
  * hook (NCCL / torch.distributed: otti_b200/comm.py). */
 int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* out);
 void sb200_comm_shm_close(sb200_comm_vt* comm);
+/* The same hook over NCCL, called natively: the bytes are staged through device memory and gathered with ncclAllGather
+ * over NVLink.  libnccl.so.2 is dlopen'ed (no link-time dependency).  Rank 0 makes the id, the host program hands it to
+ * the other ranks (128 bytes), every rank opens.  Provided so that the shared-memory hook can be measured against it. */
+int sb200_comm_nccl_unique_id(uint8_t id128[128]);
+int sb200_comm_nccl_open(const uint8_t id128[128], int rank, int world, sb200_comm_vt* out);
+void sb200_comm_nccl_close(sb200_comm_vt* comm);
 /* Host-only self-test of a hook (no GPU): `rounds` all-gathers of 3 scalars per rank, summed mod l as a sharded
  * sum-check round does; the digest must equal sb200_comm_selftest_expected(world, rounds) on every rank. */
 int sb200_comm_selftest(const sb200_comm_vt* comm, int rounds, uint8_t digest32_out[32]);

@@ -39,6 +39,34 @@ class ShmComm:
             pass
 
 
+class NcclNativeComm:
+    """`sb200_comm_nccl_open`: ncclAllGather called from inside libspartan_b200 (no Python in the loop).  The unique id
+    travels through torch.distributed once, at construction."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        ids = [None]
+        if self.rank == 0:
+            buf = (C.c_uint8 * 128)()
+            _check(lib().sb200_comm_nccl_unique_id(buf))
+            ids = [bytes(buf)]
+        dist.broadcast_object_list(ids, src=0, group=group)
+        self.vt = CommVT()
+        idbuf = (C.c_uint8 * 128).from_buffer_copy(ids[0])
+        _check(lib().sb200_comm_nccl_open(idbuf, C.c_int(self.rank), C.c_int(self.world), C.byref(self.vt)))
+
+    def close(self):
+        if self.vt.ctx:
+            lib().sb200_comm_nccl_close(C.byref(self.vt))
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class DistComm:
     """All-gather through `torch.distributed` (group=None: the default group).
 

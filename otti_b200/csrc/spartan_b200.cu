@@ -675,6 +675,7 @@ void sb200_gens_free(sb200_gens* h) { delete reinterpret_cast<Gens*>(h); }
 
 // =============================================================================== prover
 #include "host/comm.hpp"
+#include "host/comm_nccl.hpp"
 #include "host/zkif.hpp"
 #include "host/circ.hpp"
 #include "host/pool.hpp"
@@ -910,6 +911,49 @@ int sb200_comm_shm_open(const char* name, int rank, int world, sb200_comm_vt* ou
   out->world = world;
   out->allgather = shm_allgather_thunk;
   return SB200_OK;
+}
+// ---- native NCCL exchange (host/comm_nccl.hpp)
+int sb200_comm_nccl_unique_id(uint8_t id128[128]) {
+  std::string err;
+  if (!id128) return SB200_ERR_ARG;
+  if (!NcclApi::get().load(err)) { set_error(err); return SB200_ERR_COMM; }
+  NcclApi::UniqueId id;
+  if (NcclApi::get().GetUniqueId(&id) != 0) { set_error("ncclGetUniqueId failed"); return SB200_ERR_COMM; }
+  memcpy(id128, id.internal, 128);
+  return SB200_OK;
+}
+int sb200_comm_nccl_open(const uint8_t id128[128], int rank, int world, sb200_comm_vt* out) {
+  if (!id128 || !out || world < 1 || rank < 0 || rank >= world) return SB200_ERR_ARG;
+  int rc = ensure_device();
+  if (rc) return rc;
+  std::string err;
+  if (!NcclApi::get().load(err)) { set_error(err); return SB200_ERR_COMM; }
+  NcclComm* c = new NcclComm();
+  c->rank = rank;
+  c->world = world;
+  NcclApi::UniqueId id;
+  memcpy(id.internal, id128, 128);
+  cudaError_t ce = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (ce == cudaSuccess) ce = cudaMalloc((void**)&c->d_send, NcclComm::kMaxBytes);
+  if (ce == cudaSuccess) ce = cudaMalloc((void**)&c->d_recv, NcclComm::kMaxBytes * (size_t)world);
+  if (ce == cudaSuccess) ce = cudaMallocHost((void**)&c->h_stage, NcclComm::kMaxBytes * ((size_t)world + 1));
+  if (ce != cudaSuccess) { set_error(std::string("nccl exchange buffers: ") + cudaGetErrorString(ce)); delete c; return SB200_ERR_CUDA; }
+  int nrc = NcclApi::get().CommInitRank(&c->comm, world, id, rank);
+  if (nrc != 0) {
+    set_error(std::string("ncclCommInitRank: ") + (NcclApi::get().GetErrorString ? NcclApi::get().GetErrorString(nrc) : "error"));
+    delete c;
+    return SB200_ERR_COMM;
+  }
+  out->ctx = c;
+  out->rank = rank;
+  out->world = world;
+  out->allgather = nccl_allgather_thunk;
+  return SB200_OK;
+}
+void sb200_comm_nccl_close(sb200_comm_vt* comm) {
+  if (!comm || !comm->ctx) return;
+  delete static_cast<NcclComm*>(comm->ctx);
+  comm->ctx = nullptr;
 }
 void sb200_comm_shm_close(sb200_comm_vt* comm) {
   if (!comm || !comm->ctx) return;
