@@ -81,8 +81,8 @@ static inline uint64_t rotl64(uint64_t x, unsigned n) { return (x << n) | (x >> 
 void keccakf_avx512(uint64_t s[25]);  // host/keccak_avx512.cpp
 static inline void keccakf_scalar(uint64_t s[25]);
 // SB200_KECCAK=avx512 selects the AVX-512 permutation (host/keccak_avx512.cpp).  It is 1.4x faster than the portable code
-// on the build container's CPU, but on the GPU boxes of this pool (Xeon, model 207) the portable code wins: three
-// alternating runs of a 2^16 proof gave 0.585 ms of critical-path hashing against 0.605 ms, so the portable code is the default.
+// on the build container's CPU (0.58 against 0.80 us), but on the GPU boxes of this pool (Xeon, model 207) the portable
+// code wins, 0.256 against 0.336 us per permutation (tools/microbench/keccak_bench.cpp), so the portable code is the default.
 static inline void keccakf(uint64_t s[25]) {
 #if defined(__x86_64__) && !defined(SB200_NO_AVX512_KECCAK)
   static const bool wide = [] {

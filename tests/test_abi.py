@@ -87,3 +87,24 @@ def test_bench_reference_arm_prints_one_json_line():
     assert line["impl"] == "reference" and line["unit"] == "constraints/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
     assert line["config"]["workload"] == "synthetic Spartan R1CS 2^14 constraints = vars, 10 inputs, NIZK::prove"  # == the GPU arm's string
+
+
+def test_keccak_variants_agree():
+    """host/hmerlin.hpp picks the portable Keccak-f by default and the AVX-512 one with SB200_KECCAK=avx512 (when the CPU has
+    it): both must give the Merlin known-answer vector and the same challenges over a long transcript."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.path.insert(0, %r); import otti_b200 as sb; t = sb.Transcript.new(b'test protocol'); "
+            "t.append_message(b'some label', b'some data'); out = t.challenge_bytes(b'challenge', 32).hex()\n"
+            "for i in range(300):\n"
+            "    t.append_message(b'l%%d' %% i, bytes(range(i %% 200)))\n"
+            "    out += t.challenge_bytes(b'c', 64 + i %% 7).hex()\n"
+            "import hashlib; print(out[:64], hashlib.sha256(out.encode()).hexdigest())") % ROOT
+    outs = []
+    for mode in ("scalar", "avx512"):
+        env = dict(os.environ, SB200_KECCAK=mode)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-500:]
+        outs.append(r.stdout.split())
+    assert outs[0][0] == "d5a21972d0d5fe320c0d263fac7fffb8145aa640af6e9bca177c03c7efcf0615"
+    assert outs[0] == outs[1]

@@ -292,3 +292,27 @@ def test_gpu_snark_full_size_properties():
     proof.verify(comm, inputs, sb.Transcript.new(LABEL), gens)
     assert O.snark_verify(comm.to_bytes(), n, oin, LABEL, got) == 0
     assert sb.SNARK.prove(inst, comm, None, vars_, inputs, gens, sb.Transcript.new(LABEL), TAPE_SEED).to_bytes() == got
+
+
+@pytest.mark.gpu
+def test_gpu_snark_doorbell_path_gives_the_same_proof():
+    """SB200_BELL=1 (round kernels launched ahead of their challenge, released through a doorbell in mapped memory) is off
+    by default; it must stay byte-identical.  The variable is read once per process, hence the subprocess."""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    case = _golden()["cases"][-1]
+    code = ("import sys; sys.path.insert(0, %r); import hashlib, otti_b200 as sb\n"
+            "inst, v, i = sb.Instance.produce_synthetic_r1cs(%d, %d, %d, %d)\n"
+            "g = sb.SNARKGens.new(%d, %d, %d, %d)\n"
+            "c = sb.SNARK.encode(inst, g)\n"
+            "p = sb.SNARK.prove(inst, c, None, v, i, g, sb.Transcript.new(b'snark_example'), bytes(range(64)))\n"
+            "p.verify(c, i, sb.Transcript.new(b'snark_example'), g)\n"
+            "print(hashlib.sha256(p.to_bytes()).hexdigest())") % (
+                root, case["num_cons"], case["num_vars"], case["num_inputs"], case["seed"], case["num_cons"], case["num_vars"],
+                case["num_inputs"], case["num_nz_entries"])
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, SB200_BELL="1"), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-800:]
+    assert r.stdout.split()[-1] == case["proof_sha256"]
