@@ -158,9 +158,26 @@ class Strobe {
     pos_ = 0;
     begin_ = 0;
   }
+  // XOR n bytes into the rate in runs (up to the end of the rate), eight bytes at a time: a 2^22 proof absorbs 2048
+  // commitment points (125 KB) between the commitment and the first challenge, byte by byte that was 0.75 ms
+  static void xor_into(uint8_t* dst, const uint8_t* src, size_t n) {
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) {
+      uint64_t a, c;
+      memcpy(&a, dst + i, 8);
+      memcpy(&c, src + i, 8);
+      a ^= c;
+      memcpy(dst + i, &a, 8);
+    }
+    for (; i < n; i++) dst[i] ^= src[i];
+  }
   void absorb(const uint8_t* d, size_t n) {
-    while (n--) {
-      b()[pos_++] ^= *d++;
+    while (n) {
+      const size_t k = n < (size_t)(RATE - pos_) ? n : (size_t)(RATE - pos_);
+      xor_into(b() + pos_, d, k);
+      pos_ = (uint8_t)(pos_ + k);
+      d += k;
+      n -= k;
       if (pos_ == RATE) permute();
     }
   }
@@ -186,9 +203,13 @@ class Strobe {
   void ad(const void* d, size_t n, bool more) { begin(2, more); absorb((const uint8_t*)d, n); }
   void prf(uint8_t* out, size_t n) {
     begin(1 | 2 | 4, false);
-    while (n--) {
-      *out++ = b()[pos_];
-      b()[pos_++] = 0;
+    while (n) {
+      const size_t k = n < (size_t)(RATE - pos_) ? n : (size_t)(RATE - pos_);
+      memcpy(out, b() + pos_, k);
+      memset(b() + pos_, 0, k);
+      pos_ = (uint8_t)(pos_ + k);
+      out += k;
+      n -= k;
       if (pos_ == RATE) permute();
     }
   }
