@@ -702,6 +702,13 @@ static inline unsigned lat_grid(size_t pairs, const ScWork& w) {
   return (unsigned)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 static constexpr unsigned kCompactBlocks = 148;  // rounds with at most one block per SM run the compact kernels
+static unsigned compact_blocks() {  // SB200_SC_COMPACT_BLOCKS: experiment knob (a large value = the compact kernels everywhere)
+  static const unsigned v = [] {
+    const char* e = getenv("SB200_SC_COMPACT_BLOCKS");
+    return e ? (unsigned)strtoul(e, nullptr, 10) : kCompactBlocks;
+  }();
+  return v;
+}
 static inline unsigned sc_grid(size_t pairs, const ScWork& w) {
   size_t g = (pairs + 255) / 256;
   size_t cap = (size_t)kSMs * 4;
@@ -719,7 +726,7 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
     else { KProf kp_("sc_cubic_lat_kernel", s); sc_cubic_lat_kernel<false><<<gl, lat_threads(), 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
-  const bool compact = g <= kCompactBlocks;
+  const bool compact = g <= compact_blocks();
   if (do_bind && compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (do_bind) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
@@ -736,7 +743,7 @@ cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, cons
     else { KProf kp_("sc_quad_lat_kernel", s); sc_quad_lat_kernel<false><<<gl, lat_threads(), 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
     return SB_LAUNCHED();
   }
-  const bool compact = g <= kCompactBlocks;
+  const bool compact = g <= compact_blocks();
   if (do_bind && compact) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<true, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (do_bind) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<true, FlInl><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (compact) { KProf kp_("sc_quad_kernel", s); sc_quad_kernel<false, FlCall><<<g, 256, 0, s>>>(Z, Q, newlen, r, w.partials, w.counter, w.result, mb); }
