@@ -209,6 +209,17 @@ struct DotBatch {
 size_t multi_dot_tmp_scalars(uint32_t nvec);
 cudaError_t k_multi_dot(const DotBatch& b, size_t n, bool final_to_mont, fl_t* tmp, fl_t* out, cudaStream_t s);
 
+// ---- Instance::new on the device (sparse_build.cu) ------------------------------------------------------------------
+// canonical -> Montgomery; *first_bad = index of the first scalar >= l, 0xFFFFFFFF if none
+cudaError_t k_to_mont_first_bad(const fl_t* in, fl_t* out, uint32_t n, unsigned int* first_bad, cudaStream_t s);
+// Stable ordering of one matrix by `keys` (row for the CSR, column for the CSC; 0xFFFFFFFF = entry of another rank; `kept`
+// real keys, all below 2^key_bits): ptr[nseg + 1], and per position the other coordinate, the Montgomery value and (op !=
+// NULL) the index of the entry in the caller's list.  tmp: sparse_build_tmp_bytes(nnz).
+size_t sparse_build_tmp_bytes(uint32_t nnz);
+cudaError_t k_sparse_build(const uint32_t* keys, const uint32_t* other, const fl_t* vals_mont, uint32_t nnz, uint32_t kept, uint32_t nseg,
+                           uint32_t key_bits, uint32_t* ptr, uint32_t* idx, fl_t* val, uint32_t* op, void* tmp, size_t tmp_bytes,
+                           cudaStream_t s);
+
 // per-kernel device time of every launch while enabled (CUDA events around each launch); report = CSV lines
 // "kernel,launches,total_ms" sorted by time, and clears the records
 void kprof_enable(bool on);

@@ -77,10 +77,6 @@ static inline Cpt cpt_from(const uint8_t* p) {
 }
 
 // ------------------------------------------------------------------------------ instance
-struct CooEntry {
-  uint32_t row, col;
-  Fl val;  // Montgomery
-};
 // vector storage that resize() leaves uninitialised (every element is written by the conversion threads)
 template <typename T>
 struct RawAlloc : std::allocator<T> {
@@ -90,7 +86,6 @@ struct RawAlloc : std::allocator<T> {
   template <typename U> void construct(U* p) { ::new ((void*)p) U; }
   template <typename U, typename... A> void construct(U* p, A&&... a) { ::new ((void*)p) U(std::forward<A>(a)...); }
 };
-typedef std::vector<CooEntry, RawAlloc<CooEntry>> CooVec;
 
 // threads for the host-side loops of Instance::new and the zkinterface reader (independent of the prover's worker pool)
 static unsigned ingest_threads(size_t items) {
@@ -107,93 +102,117 @@ static void run_threads(unsigned n, F&& f) {  // f(t) for t < n, f(0) on the cal
   for (auto& x : th) x.join();
 }
 
-// One (orientation, matrix) of the device form: stable counting sort of the caller's entries by row (CSR) or column (CSC),
-// the op index each position came from (SNARK mode), and the chunk lists of the long segments.  Host only.
-struct SparseHost {
-  std::vector<uint32_t> ptr, idx, op, lseg, lfirst, lo, hi, big;
-  std::vector<Fl> val;
-};
-static void sort_sparse(const CooVec& M, int orient, uint64_t nseg, uint32_t g, uint32_t k, uint32_t sh, SparseHost& o) {
-  o.ptr.assign(nseg + 1, 0);
+// One matrix in the caller's entry order: 32-bit global coordinates (the columns already moved to the padded z layout) and
+// the values, either the caller's canonical 32-byte scalars or Montgomery limbs (the synthetic generator).
+typedef std::vector<uint32_t, RawAlloc<uint32_t>> U32Vec;
+static_assert(sizeof(Fl) == 32 && sizeof(sb::fl_t) == 32, "scalars travel to the device as 8 x u32");
+struct CooHost {
+  U32Vec rows, cols;
+  const uint8_t* canon = nullptr;
+  const Fl* mont = nullptr;
   size_t nnz = 0;
-  for (const CooEntry& e : M) {
-    uint32_t key = orient == 0 ? e.row : e.col;
-    if ((key & (g - 1)) != k) continue;
-    o.ptr[(key >> sh) + 1]++;
-    nnz++;
-  }
-  o.idx.resize(nnz);
-  o.op.resize(g == 1 ? nnz : 0);
-  o.val.resize(nnz);
-  for (uint64_t i = 0; i < nseg; i++) o.ptr[i + 1] += o.ptr[i];
-  std::vector<uint32_t> fill(o.ptr.begin(), o.ptr.end() - 1);
-  uint32_t opi = 0;
-  for (const CooEntry& e : M) {
-    const uint32_t this_op = opi++;
-    uint32_t key = orient == 0 ? e.row : e.col;
-    if ((key & (g - 1)) != k) continue;
-    uint32_t at = fill[key >> sh]++;  // stable: entries of a segment keep the caller's order
-    o.idx[at] = orient == 0 ? e.col : e.row;  // the other coordinate stays global
-    o.val[at] = e.val;
-    if (g == 1) o.op[at] = this_op;
-  }
-  // long segments -> chunk lists (dev.hpp LongSegs)
+};
+// long segments of one sorted (orientation, matrix) -> chunk lists (dev.hpp LongSegs), from the segment pointers
+static int upload_long_segs(const std::vector<uint32_t>& ptr, uint64_t nseg, SparseDev& sd, int m) {
+  std::vector<uint32_t> lseg, lfirst, lo, hi, big;
   for (uint64_t sgm = 0; sgm < nseg; sgm++) {
-    const uint32_t a = o.ptr[sgm], b = o.ptr[sgm + 1];
+    const uint32_t a = ptr[sgm], b = ptr[sgm + 1];
     if (b - a <= sb::kLongSeg) continue;
-    o.lseg.push_back((uint32_t)sgm);
-    o.lfirst.push_back((uint32_t)o.lo.size());
-    for (uint32_t q = a; q < b; q += sb::kSegChunk) { o.lo.push_back(q); o.hi.push_back(std::min(b, q + sb::kSegChunk)); }
-    if (o.lo.size() - o.lfirst.back() > sb::kSumInline) o.big.push_back((uint32_t)o.lseg.size() - 1);
+    lseg.push_back((uint32_t)sgm);
+    lfirst.push_back((uint32_t)lo.size());
+    for (uint32_t q = a; q < b; q += sb::kSegChunk) { lo.push_back(q); hi.push_back(std::min(b, q + sb::kSegChunk)); }
+    if (lo.size() - lfirst.back() > sb::kSumInline) big.push_back((uint32_t)lseg.size() - 1);
   }
-  o.lfirst.push_back((uint32_t)o.lo.size());
-}
-static int upload_one(const SparseHost& h, int orient, int m, uint64_t nseg, uint32_t g, Instance& inst) {
-  SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
-  const size_t nnz = h.idx.size();
-  if (g == 1) {
-    DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
-    SB_CUDA(od.alloc(nnz ? nnz : 1));
-    if (nnz) SB_CUDA(cudaMemcpy(od.p, h.op.data(), nnz * 4, cudaMemcpyHostToDevice));
-  }
-  sd.nlong[m] = (uint32_t)h.lseg.size(); sd.nchunks[m] = (uint32_t)h.lo.size(); sd.nbig[m] = (uint32_t)h.big.size();
+  lfirst.push_back((uint32_t)lo.size());
+  sd.nlong[m] = (uint32_t)lseg.size(); sd.nchunks[m] = (uint32_t)lo.size(); sd.nbig[m] = (uint32_t)big.size();
   auto put = [](DevBuf<uint32_t>& d, const std::vector<uint32_t>& v) -> cudaError_t {
     cudaError_t e = d.alloc(v.size() ? v.size() : 1);
     if (e != cudaSuccess || v.empty()) return e;
     return cudaMemcpy(d.p, v.data(), v.size() * 4, cudaMemcpyHostToDevice);
   };
-  SB_CUDA(put(sd.lg_seg[m], h.lseg)); SB_CUDA(put(sd.lg_first[m], h.lfirst)); SB_CUDA(put(sd.lg_lo[m], h.lo));
-  SB_CUDA(put(sd.lg_hi[m], h.hi)); SB_CUDA(put(sd.lg_big[m], h.big));
-  SB_CUDA(sd.lg_partial[m].alloc(h.lo.size() ? h.lo.size() : 1));
-  SB_CUDA(sd.lg_reduced[m].alloc(h.lseg.size() ? h.lseg.size() : 1));
-  SB_CUDA(sd.ptr[m].alloc(nseg + 1));
-  SB_CUDA(sd.idx[m].alloc(nnz ? nnz : 1));
-  SB_CUDA(sd.val[m].alloc(nnz ? nnz : 1));
-  SB_CUDA(cudaMemcpy(sd.ptr[m].p, h.ptr.data(), (nseg + 1) * 4, cudaMemcpyHostToDevice));
-  if (nnz) {
-    SB_CUDA(cudaMemcpy(sd.idx[m].p, h.idx.data(), nnz * 4, cudaMemcpyHostToDevice));
-    SB_CUDA(cudaMemcpy(sd.val[m].p, h.val.data(), nnz * 32, cudaMemcpyHostToDevice));
-  }
+  SB_CUDA(put(sd.lg_seg[m], lseg)); SB_CUDA(put(sd.lg_first[m], lfirst)); SB_CUDA(put(sd.lg_lo[m], lo));
+  SB_CUDA(put(sd.lg_hi[m], hi)); SB_CUDA(put(sd.lg_big[m], big));
+  SB_CUDA(sd.lg_partial[m].alloc(lo.size() ? lo.size() : 1));
+  SB_CUDA(sd.lg_reduced[m].alloc(lseg.size() ? lseg.size() : 1));
   return SB200_OK;
 }
-static int upload_sparse(const CooVec M[3], uint64_t nrows, uint64_t ncols, Instance& inst) {
+// The device form of the three matrices: CSR by constraint row and CSC by z column, both stable in the caller's entry
+// order, built by sparse_build.cu from one upload of each matrix.  bad_scalar[m] receives the index of the first scalar
+// >= l of matrix m (0xFFFFFFFF if none); the build stops at the first matrix that has one.
+static int upload_sparse(const CooHost M[3], uint64_t nrows, uint64_t ncols, Instance& inst, uint32_t bad_scalar[3]) {
   const uint32_t g = (uint32_t)inst.world, k = (uint32_t)inst.rank, sh = inst.gamma;
-  // the six sorts are independent: one thread each when the matrices are large (0.84 -> 0.2 s for the Otti-shaped 2^20
-  // instance of bench.py); the uploads follow on the calling thread
-  SparseHost H[2][3];
-  const size_t total = M[0].size() + M[1].size() + M[2].size();
-  // the six (orientation, matrix) sorts are independent: one thread each when the matrices are large; the uploads then
-  // follow on the calling thread (pageable copies issued from several threads at once serialise in the driver and came
-  // out 2x slower than this on the Otti-shaped 2^20 instance)
-  auto task = [&](unsigned q) { sort_sparse(M[q % 3], (int)(q / 3), (q / 3 == 0 ? nrows : ncols) >> sh, g, k, sh, H[q / 3][q % 3]); };
-  if (ingest_threads(total) >= 6) run_threads(6, task);
-  else if (ingest_threads(total) >= 2) run_threads(2, [&](unsigned t) { for (unsigned q = t; q < 6; q += 2) task(q); });
-  else for (unsigned q = 0; q < 6; q++) task(q);
-  for (unsigned q = 0; q < 6; q++) {
-    const int orient = (int)(q / 3), m = (int)(q % 3);
-    int rc = upload_one(H[orient][m], orient, m, (orient == 0 ? nrows : ncols) >> sh, g, inst);
-    if (rc) return rc;
-    H[orient][m] = SparseHost();  // release the host copy
+  for (int m = 0; m < 3; m++) bad_scalar[m] = 0xFFFFFFFFu;
+  cudaStream_t s = 0;
+  for (int m = 0; m < 3; m++) {
+    const size_t nnz = M[m].nnz;
+    const uint32_t n32 = (uint32_t)nnz;
+    DevBuf<uint32_t> d_rows, d_cols, d_key, d_bad;
+    DevBuf<sb::fl_t> d_in, d_mont;
+    DevBuf<uint8_t> d_tmp;
+    const size_t tmp_bytes = sb::sparse_build_tmp_bytes(n32);
+    SB_CUDA(d_rows.alloc(nnz ? nnz : 1)); SB_CUDA(d_cols.alloc(nnz ? nnz : 1)); SB_CUDA(d_bad.alloc(1));
+    SB_CUDA(d_mont.alloc(nnz ? nnz : 1)); SB_CUDA(d_tmp.alloc(tmp_bytes));
+    if (g > 1) SB_CUDA(d_key.alloc(nnz ? nnz : 1));
+    if (nnz) {
+      SB_CUDA(cudaMemcpyAsync(d_rows.p, M[m].rows.data(), nnz * 4, cudaMemcpyHostToDevice, s));
+      SB_CUDA(cudaMemcpyAsync(d_cols.p, M[m].cols.data(), nnz * 4, cudaMemcpyHostToDevice, s));
+    }
+    if (M[m].canon != nullptr) {
+      SB_CUDA(d_in.alloc(nnz ? nnz : 1));
+      if (nnz) SB_CUDA(cudaMemcpyAsync(d_in.p, M[m].canon, nnz * 32, cudaMemcpyHostToDevice, s));
+      SB_CUDA(sb::k_to_mont_first_bad(d_in.p, d_mont.p, n32, d_bad.p, s));
+      SB_CUDA(cudaMemcpyAsync(&bad_scalar[m], d_bad.p, 4, cudaMemcpyDeviceToHost, s));
+    } else if (nnz) {
+      SB_CUDA(cudaMemcpyAsync(d_mont.p, M[m].mont, nnz * 32, cudaMemcpyHostToDevice, s));
+    }
+    for (int orient = 0; orient < 2; orient++) {
+      SparseDev& sd = orient == 0 ? inst.csr : inst.csc;
+      const uint64_t nseg = (orient == 0 ? nrows : ncols) >> sh;
+      const U32Vec& coord = orient == 0 ? M[m].rows : M[m].cols;
+      const uint32_t* d_coord = orient == 0 ? d_rows.p : d_cols.p;
+      const uint32_t* d_other = orient == 0 ? d_cols.p : d_rows.p;
+      size_t kept = nnz;
+      const uint32_t* d_keys = d_coord;
+      U32Vec keys;
+      if (g > 1) {  // this rank keeps the segments congruent to its rank; the other entries sort behind them
+        keys.resize(nnz);
+        const unsigned T = ingest_threads(nnz);
+        std::vector<size_t> cnt(T, 0);
+        run_threads(T, [&](unsigned t) {
+          size_t c = 0;
+          for (size_t i = nnz * t / T, e = nnz * (t + 1) / T; i < e; i++) {
+            const uint32_t key = coord[i];
+            const bool mine = (key & (g - 1)) == k;
+            keys[i] = mine ? key >> sh : 0xFFFFFFFFu;
+            c += mine;
+          }
+          cnt[t] = c;
+        });
+        kept = 0;
+        for (size_t c : cnt) kept += c;
+        if (nnz) SB_CUDA(cudaMemcpyAsync(d_key.p, keys.data(), nnz * 4, cudaMemcpyHostToDevice, s));
+        d_keys = d_key.p;
+      }
+      uint32_t key_bits = 1;
+      while (key_bits < 32 && ((uint64_t)1 << key_bits) < nseg) key_bits++;
+      uint32_t* d_op = nullptr;
+      if (g == 1) {  // SNARK mode reads the op each position came from
+        DevBuf<uint32_t>& od = orient == 0 ? inst.op_csr[m] : inst.op_csc[m];
+        SB_CUDA(od.alloc(kept ? kept : 1));
+        d_op = od.p;
+      }
+      SB_CUDA(sd.ptr[m].alloc(nseg + 1));
+      SB_CUDA(sd.idx[m].alloc(kept ? kept : 1));
+      SB_CUDA(sd.val[m].alloc(kept ? kept : 1));
+      SB_CUDA(sb::k_sparse_build(d_keys, d_other, d_mont.p, n32, (uint32_t)kept, (uint32_t)nseg, key_bits, sd.ptr[m].p, sd.idx[m].p,
+                                 sd.val[m].p, d_op, d_tmp.p, tmp_bytes, s));
+      std::vector<uint32_t> ptr(nseg + 1);
+      SB_CUDA(cudaMemcpyAsync(ptr.data(), sd.ptr[m].p, (nseg + 1) * 4, cudaMemcpyDeviceToHost, s));
+      SB_CUDA(cudaStreamSynchronize(s));  // also keeps `keys` alive until its copy is done
+      if (bad_scalar[m] != 0xFFFFFFFFu) return SB200_OK;  // the caller reports InvalidScalar
+      int rc = upload_long_segs(ptr, nseg, sd, m);
+      if (rc) return rc;
+    }
   }
   return SB200_OK;
 }
@@ -274,39 +293,56 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
     fprintf(stderr, "[sb200-instance] %8.3f ms  %s\n", (t - it0) * 1e3, what);
     it0 = t;
   };
-  CooVec M[3];
+  CooHost M[3];
+  uint64_t bad_at[3] = {~0ull, ~0ull, ~0ull};
+  int bad_code[3] = {0, 0, 0};
+  bool any_bad = false;
   for (int m = 0; m < 3; m++) {
     if (nnz[m] >= (1ull << 32)) return SB200_ERR_ARG;
-    M[m].resize(nnz[m]);
-    // entries are checked and converted in slices; the error reported is the one the reference meets first (lowest entry)
+    M[m].nnz = nnz[m];
+    M[m].canon = vals32[m];
+    M[m].rows.resize(nnz[m]);
+    M[m].cols.resize(nnz[m]);
+    // the indices are checked and narrowed in slices on the host; the scalars are checked by the kernel that converts them
     const unsigned T = ingest_threads(nnz[m]);
-    std::vector<uint64_t> bad_at(T, ~0ull);
-    std::vector<int> bad_code(T, 0);
+    std::vector<uint64_t> t_bad(T, ~0ull);
+    std::vector<int> t_code(T, 0);
     run_threads(T, [&](unsigned t) {
       const uint64_t k0 = nnz[m] * t / T, k1 = nnz[m] * (t + 1) / T;
       for (uint64_t k = k0; k < k1; k++) {
         uint64_t row = rows[m][k], col = cols[m][k];
         int code = 0;
-        Fl v = fl_zero();
         if (row >= num_cons) code = 1;                                    // lib.rs:166-168
         else if (col >= num_vars + 1 + num_inputs) code = 2;              // lib.rs:171-173
-        else if (!fl_from_bytes(vals32[m] + 32 * k, v)) code = 3;         // lib.rs:175-187
-        if (code) { bad_at[t] = k; bad_code[t] = code; return; }
+        if (code) { t_bad[t] = k; t_code[t] = code; return; }
         if (col >= num_vars) col += nvp - num_vars;  // 1 and the inputs live in the second half of z, lib.rs:180-181
-        M[m][k] = CooEntry{(uint32_t)row, (uint32_t)col, v};
+        M[m].rows[k] = (uint32_t)row;
+        M[m].cols[k] = (uint32_t)col;
       }
     });
     for (unsigned t = 0; t < T; t++) {
-      if (bad_at[t] == ~0ull) continue;
-      if (bad_code[t] == 1) { set_error("InvalidIndex: row"); return SB200_ERR_INVALID_INDEX; }
-      if (bad_code[t] == 2) { set_error("InvalidIndex: col"); return SB200_ERR_INVALID_INDEX; }
-      set_error("InvalidScalar");
-      return SB200_ERR_INVALID_SCALAR;
+      if (t_bad[t] == ~0ull) continue;
+      bad_at[m] = t_bad[t]; bad_code[m] = t_code[t]; any_bad = true;
+      break;
     }
     // lib.rs:191-197 appends zero-valued entries when num_cons is 0 or 1; they contribute nothing to any product
     // (SNARK::encode would see them as ops: Instance::pad_entries makes sb200_snark_encode refuse such an instance).
   }
-  imark("entries checked and converted");
+  if (any_bad) {
+    // the error reported is the one the reference meets first: matrices in order, entries in order, and for one entry the
+    // row, the column, then the scalar (lib.rs:163-187).  Only this path reads the scalars on the host.
+    for (int m = 0; m < 3; m++) {
+      const uint64_t end = bad_at[m] == ~0ull ? nnz[m] : bad_at[m];
+      for (uint64_t k = 0; k < end; k++) {
+        Fl v;
+        if (!fl_from_bytes(vals32[m] + 32 * k, v)) { set_error("InvalidScalar"); return SB200_ERR_INVALID_SCALAR; }
+      }
+      if (bad_at[m] == ~0ull) continue;
+      set_error(bad_code[m] == 1 ? "InvalidIndex: row" : "InvalidIndex: col");
+      return SB200_ERR_INVALID_INDEX;
+    }
+  }
+  imark("indices checked and narrowed");
   uint32_t gamma = 0;
   int rc = shard_check(rank, world, ncp, nvp, gamma);
   if (rc) return rc;
@@ -315,11 +351,18 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
   Instance* inst = new Instance();
   inst->num_cons = ncp; inst->num_vars = nvp; inst->num_inputs = num_inputs;
   inst->rank = rank; inst->world = world; inst->gamma = gamma;
-  for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].size();
+  for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].nnz;
   inst->pad_entries = num_cons == 0 || num_cons == 1;
-  rc = upload_sparse(M, ncp, 2 * nvp, *inst);
+  uint32_t bad_scalar[3];
+  rc = upload_sparse(M, ncp, 2 * nvp, *inst, bad_scalar);
   if (rc) { delete inst; return rc; }
-  imark("CSR / CSC sorted and uploaded");
+  for (int m = 0; m < 3; m++)
+    if (bad_scalar[m] != 0xFFFFFFFFu) {  // lib.rs:175-187
+      delete inst;
+      set_error("InvalidScalar");
+      return SB200_ERR_INVALID_SCALAR;
+    }
+  imark("scalars converted, CSR / CSC ordered on the device");
   *out = reinterpret_cast<sb200_instance*>(inst);
   return SB200_OK;
 }
@@ -377,21 +420,28 @@ int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint6
     Zinv[i] = fl_mul(acc, pre[i]);
     acc = fl_mul(acc, Z[i]);
   }
-  CooVec M[3];
-  for (int m = 0; m < 3; m++) M[m].reserve(num_cons);
+  CooHost M[3];
+  FlVec V[3];
+  for (int m = 0; m < 3; m++) {
+    M[m].nnz = num_cons;
+    M[m].rows.resize(num_cons); M[m].cols.resize(num_cons); V[m].resize(num_cons);
+  }
   for (uint64_t i = 0; i < num_cons; i++) {
     uint64_t ai = i % size_z, bi = (i + 2) % size_z, ci = (i + 3) % size_z;
-    M[0].push_back(CooEntry{(uint32_t)i, (uint32_t)ai, fl_one()});
-    M[1].push_back(CooEntry{(uint32_t)i, (uint32_t)bi, fl_one()});
+    for (int m = 0; m < 3; m++) M[m].rows[i] = (uint32_t)i;
+    M[0].cols[i] = (uint32_t)ai; V[0][i] = fl_one();
+    M[1].cols[i] = (uint32_t)bi; V[1][i] = fl_one();
     Fl ab = fl_mul(Z[ai], Z[bi]);
-    if (Z[ci].is_zero()) M[2].push_back(CooEntry{(uint32_t)i, (uint32_t)num_vars, ab});
-    else M[2].push_back(CooEntry{(uint32_t)i, (uint32_t)ci, fl_mul(ab, Zinv[ci])});
+    if (Z[ci].is_zero()) { M[2].cols[i] = (uint32_t)num_vars; V[2][i] = ab; }
+    else { M[2].cols[i] = (uint32_t)ci; V[2][i] = fl_mul(ab, Zinv[ci]); }
   }
+  for (int m = 0; m < 3; m++) M[m].mont = V[m].data();
   Instance* inst = new Instance();
   inst->num_cons = num_cons; inst->num_vars = num_vars; inst->num_inputs = num_inputs;
   inst->rank = rank; inst->world = world; inst->gamma = gamma;
-  for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].size();
-  rc = upload_sparse(M, num_cons, 2 * num_vars, *inst);
+  for (int m = 0; m < 3; m++) inst->nnz[m] = M[m].nnz;
+  uint32_t bad_scalar[3];
+  rc = upload_sparse(M, num_cons, 2 * num_vars, *inst, bad_scalar);
   if (rc) { delete inst; return rc; }
   for (uint64_t i = 0; i < num_vars; i++) fl_to_bytes(Z[i], vars32_out + 32 * i);
   for (uint64_t i = 0; i < num_inputs; i++) fl_to_bytes(Z[num_vars + 1 + i], inputs32_out + 32 * i);
