@@ -138,6 +138,11 @@ struct ScWork {
 cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind, fl_t r, const ScWork& w,
                        cudaStream_t s);
 // Same for the quadratic sum-check (sumcheck.rs:453-484): result = e0, e2, (0)
+// phase one with eq(tau) factored out (kernels.cu sc_cubic_eq_kernel): pyramids of suffix eq tables, one factored round
+bool sc_round_is_long(size_t pairs, const ScWork& w);
+cudaError_t k_eq_pyramid(const fl_t* tau, uint32_t m, uint32_t lo_bits, fl_t init, fl_t* lo, fl_t* hi, cudaStream_t s);
+cudaError_t k_sc_cubic_eq(const fl_t* lo, const fl_t* hi, uint32_t lo_bits, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind,
+                          fl_t r, const ScWork& w, cudaStream_t s);
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s);
 
 // LZ[i] = sum_j Lv[j] * Z[j*R + i]                                    (dense_mlpoly.rs:205-212)

@@ -543,6 +543,69 @@ __global__ void __launch_bounds__(256, 2) sc_quad_kernel(fl_t* __restrict__ Z, f
   }
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
+// ---- phase one with eq(tau) factored out of the round polynomial ------------------------------------------------------
+// Round j of prove_cubic_with_additive_term (sumcheck.rs:618-674) sums T*(A*B - C) over the table halves with
+// T = eq(tau) bound at r_0..r_{j-1}.  T is a product: T[b*h + x] = S_j * eq(tau_j, b) * E_j[x], S_j = prod_k eq(tau_k, r_k)
+// and E_j = eq(tau_{j+1}.., x), so the round polynomial is s_j(X) = S_j * eq(tau_j, X) * q_j(X) with the QUADRATIC
+//     q_j(X) = sum_x E_j[x] * (A(X,x) * B(X,x) - C(X,x)).
+// The kernel returns q_j(0) and q_j's leading coefficient sum_x E_j[x] * dA * dB; the host gets q_j(1) from the running
+// claim and evaluates s_j at 0, 2, 3 (prover.inc EqFactor) -- the same field elements the reference computes, with 4
+// instead of 6 products per pair, and T is neither read nor bound (8 -> 6 bind products, 24h -> 18h scalars moved).
+// E_j[x] = HI[x >> lo_bits] * LO[x & mask]: a thread's pairs all share x & mask (lo_bits <= 8, 256 threads per block), so
+// it multiplies by HI inside the loop and by LO once at the end.  The tables of every round come from one small launch:
+// eq_pyramid_kernel writes, for t = 0..bits, eq over the LAST t variables of its range at offset 2^t - 1.
+__global__ void eq_pyramid_kernel(const fl_t* __restrict__ tau, uint32_t m, uint32_t lo_bits, uint32_t hi_bits, fl_t init,
+                                  fl_t* __restrict__ lo, fl_t* __restrict__ hi) {
+  const uint32_t nlo = (2u << lo_bits) - 1, nhi = (2u << hi_bits) - 1;
+  uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= nlo + nhi) return;
+  const bool is_hi = p >= nlo;
+  if (is_hi) p -= nlo;
+  const uint32_t t = 31 - __clz(p + 1), x = p + 1 - (1u << t);
+  const uint32_t end = is_hi ? m - lo_bits : m;  // the table covers tau[end - t .. end)
+  fl_t acc = is_hi ? fl_one() : init;
+  const fl_t one = fl_one();
+  for (uint32_t k = 0; k < t; k++) {
+    const fl_t rk = ldg_fl(tau + end - t + k);
+    const bool bit = (x >> (t - 1 - k)) & 1u;
+    acc = fl_mul(acc, bit ? rk : fl_sub(one, rk));
+  }
+  st_fl((is_hi ? hi : lo) + p, acc);
+}
+template <bool BIND, class M>
+__global__ void __launch_bounds__(256, 2) sc_cubic_eq_kernel(const fl_t* __restrict__ lo_tab, const fl_t* __restrict__ hi_tab,
+                                                          uint32_t lo_bits, fl_t* __restrict__ A, fl_t* __restrict__ B,
+                                                          fl_t* __restrict__ C, size_t newlen, fl_t r, fl_t* partials,
+                                                          unsigned int* counter, fl_t* result, Mailbox mb) {
+  __shared__ fl_t smem[3 * 32];
+  const size_t h = newlen >> 1;
+  fl_t e[3];
+  e[0] = e[1] = e[2] = fl_zero();
+  fl_t* tabs[3] = {A, B, C};
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < h; i += (size_t)gridDim.x * blockDim.x) {
+    fl_t lo[3], hi[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      fl_t* X = tabs[k];
+      if (BIND) {
+        lo[k] = bind1<M>(ld_fl(X + i), ld_fl(X + i + newlen), r);
+        hi[k] = bind1<M>(ld_fl(X + i + h), ld_fl(X + i + h + newlen), r);
+        st_fl(X + i, lo[k]);
+        st_fl(X + i + h, hi[k]);
+      } else {
+        lo[k] = ld_fl(X + i);
+        hi[k] = ld_fl(X + i + h);
+      }
+    }
+    const fl_t hy = ldg_fl(hi_tab + (i >> lo_bits));
+    e[0] = fl_add(e[0], M::mul(hy, fl_sub(M::mul(lo[0], lo[1]), lo[2])));
+    e[1] = fl_add(e[1], M::mul(hy, M::mul(fl_sub(hi[0], lo[0]), fl_sub(hi[1], lo[1]))));
+  }
+  const fl_t lx = ldg_fl(lo_tab + (threadIdx.x & ((1u << lo_bits) - 1)));
+  e[0] = M::mul(e[0], lx);
+  e[1] = M::mul(e[1], lx);
+  grid_sum_fl<3>(e, smem, partials, counter, result, mb);
+}
 // ---- latency variants for the short rounds --------------------------------------------------
 // A short round is one pass of ~14 dependent field multiplications per thread in the kernels above: ~25 us however
 // little data there is.  Here FOUR threads share a pair: each binds one table (cubic) or one table half (quadratic),
@@ -731,6 +794,32 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   else if (do_bind) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  return SB_LAUNCHED();
+}
+// rounds with this many pairs run sc_cubic_kernel / sc_quad_kernel (the others the four-lane latency variants)
+bool sc_round_is_long(size_t pairs, const ScWork& w) { return !(pairs <= lat_pairs_setting() && w.max_blocks >= kLatPairs / 64); }
+cudaError_t k_eq_pyramid(const fl_t* tau, uint32_t m, uint32_t lo_bits, fl_t init, fl_t* lo, fl_t* hi, cudaStream_t s) {
+  const uint32_t hi_bits = m - 1 - lo_bits, n = (2u << lo_bits) + (2u << hi_bits) - 2;
+  { KProf kp_("eq_pyramid_kernel", s); eq_pyramid_kernel<<<(n + 127) / 128, 128, 0, s>>>(tau, m, lo_bits, hi_bits, init, lo, hi); }
+  return SB_LAUNCHED();
+}
+// One factored round: the tables hold n_old entries (m_now = log2 of the length after this launch's bind); lo / hi are the
+// pyramids of k_eq_pyramid built with the same lo_bits over the m variables of the unbound tables.
+cudaError_t k_sc_cubic_eq(const fl_t* lo, const fl_t* hi, uint32_t lo_bits, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind,
+                          fl_t r, const ScWork& w, cudaStream_t s) {
+  const size_t newlen = do_bind ? n_old / 2 : n_old, h = newlen / 2;
+  uint32_t nv = 0;  // variables of E: h = 2^nv
+  while (((size_t)1 << nv) < h) nv++;
+  const uint32_t lb = nv < lo_bits ? nv : lo_bits, u = nv - lb;
+  const fl_t* lo_tab = lo + (((size_t)1 << lb) - 1);
+  const fl_t* hi_tab = hi + (((size_t)1 << u) - 1);
+  unsigned g = sc_grid(h, w);
+  Mailbox mb{w.host_result, w.host_flag, w.seq};
+  const bool compact = g <= compact_blocks();
+  if (do_bind && compact) { KProf kp_("sc_cubic_eq_kernel", s); sc_cubic_eq_kernel<true, FlCall><<<g, 256, 0, s>>>(lo_tab, hi_tab, lb, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (do_bind) { KProf kp_("sc_cubic_eq_kernel", s); sc_cubic_eq_kernel<true, FlInl><<<g, 256, 0, s>>>(lo_tab, hi_tab, lb, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else if (compact) { KProf kp_("sc_cubic_eq_kernel", s); sc_cubic_eq_kernel<false, FlCall><<<g, 256, 0, s>>>(lo_tab, hi_tab, lb, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  else { KProf kp_("sc_cubic_eq_kernel", s); sc_cubic_eq_kernel<false, FlInl><<<g, 256, 0, s>>>(lo_tab, hi_tab, lb, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   return SB_LAUNCHED();
 }
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s) {

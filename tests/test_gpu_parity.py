@@ -409,6 +409,36 @@ def test_nizk_prove_ragged(sb, dims):
         assert not pi.is_sat(sb.VarsAssignment.new(bad), pin)
 
 
+def test_first_error_wins_like_the_reference(sb):
+    """Instance::new reports the failure it meets first: matrices in order, entries in order, row/column before the scalar
+    (lib.rs:163-187).  The library checks indices on the host and scalars on the device; the oracle is the judge."""
+    zero, one = bytes(32), bytes([1]) + bytes(31)
+    larger = bytes([0xEE] * 32)
+    ok = [(k % 4, k % 8, one) for k in range(12)]
+
+    def with_(base, at, entry):
+        L = list(base)
+        L[at] = entry
+        return L
+
+    bad_s, bad_r, bad_c = (1, 1, larger), (4, 1, zero), (1, 10, zero)
+    cases = [
+        (with_(ok, 5, bad_s)[:9] + [bad_r] + ok[10:], ok, ok),          # A: scalar at 5, row at 9
+        (with_(ok, 3, bad_c)[:7] + [bad_s] + ok[8:], ok, ok),           # A: column at 3, scalar at 7
+        (ok, with_(ok, 11, bad_s), with_(ok, 0, bad_r)),                # B scalar before C row
+        (with_(ok, 11, bad_s), with_(ok, 0, bad_r), ok),                # A scalar (late) before B row (early)
+        (ok, with_(ok, 2, bad_r), with_(ok, 1, bad_s)),                 # B row before C scalar
+        (ok, ok, with_(ok, 6, (4, 1, larger))),                         # one entry with both: the row is checked first
+        (ok, ok, with_(ok, 6, bad_s)),
+    ]
+    for A, B, Cm in cases:
+        with pytest.raises(ValueError) as oe:
+            O.Instance.new(4, 8, 1, A, B, Cm)
+        with pytest.raises(sb.R1CSError) as e:
+            sb.Instance.new(4, 8, 1, A, B, Cm)
+        assert e.value.kind in str(oe.value), (e.value.kind, str(oe.value))
+
+
 def test_error_behaviour(sb):
     """check_r1cs_invalid_index / check_r1cs_invalid_scalar (lib.rs:607-650) and prove's asserts."""
     zero = bytes(32)
@@ -629,3 +659,32 @@ def test_full_size_properties(sb, s):
     vb = bytearray(bytes(pv.data))
     vb[0] ^= 1
     assert not pi.is_sat(sb.VarsAssignment.new(bytes(vb)), pin)
+
+
+@pytest.mark.parametrize("env", [{"SB200_SC_LAT_PAIRS": "0"}, {"SB200_SC_LAT_PAIRS": "0", "SB200_HOST_TAIL_LOG": "0"},
+                                 {"SB200_SC_EQ_FACTOR": "0"}])
+def test_factored_first_sumcheck_gives_the_same_proof(env):
+    """Phase one's long rounds run with eq(tau) factored out of the round polynomial (kernels.cu sc_cubic_eq_kernel,
+    prover.inc EqFactor).  By default that covers the rounds above 8192 pairs (instances from 2^15 on, which the full-size
+    tests compare with the oracle); here SB200_SC_LAT_PAIRS=0 pushes every device round of small instances through it, and
+    SB200_SC_EQ_FACTOR=0 switches it off: the proof bytes stay the oracle's (sumcheck.rs:618-674).  The variables are read
+    once per process, hence the subprocess."""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shapes = [(1 << 12, 1 << 12, 10), (1 << 13, 1 << 12, 3), (1 << 14, 1 << 15, 100), (1 << 16, 1 << 16, 10)]
+    want = []
+    for nc, nv, ni in shapes:
+        oi, ov, oin = O.Instance.synthetic(nc, nv, ni, 0x5eed)
+        want.append(hashlib.sha256(O.nizk_prove(oi, ov, oin, O.Gens(nc, nv, ni), LABEL, TAPE_SEED, 8)).hexdigest())
+    code = ("import sys; sys.path.insert(0, %r); import hashlib, otti_b200 as sb\n"
+            "for nc, nv, ni in %r:\n"
+            "    inst, v, i = sb.Instance.produce_synthetic_r1cs(nc, nv, ni, 0x5eed)\n"
+            "    g = sb.NIZKGens.new(nc, nv, ni)\n"
+            "    p = sb.NIZK.prove(inst, v, i, g, sb.Transcript.new(%r), bytes(%r))\n"
+            "    print(hashlib.sha256(p.to_bytes()).hexdigest())\n") % (root, shapes, LABEL, list(TAPE_SEED))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-800:]
+    assert r.stdout.split()[-len(shapes):] == want
