@@ -299,7 +299,7 @@ def roofline_for(kernel, kernel_s, share, s, c, sm_mhz, extra=None):
                     "frac": alg_bytes / kernel_s / 1e9 / hbm_peak if kernel_s > 0 else 0.0, "peak_source": which},
         })
     else:
-        ntab = 4 if "cubic" in kernel else 2
+        ntab = 3 if "cubic_eq" in kernel else 4 if "cubic" in kernel else 2
         rec.update({"bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": which, "achieved": None, "frac": None,
                     "note": "per-round bytes = %d tables x 32 B x 1.5 n; see hbm_kernel_sample for round 0" % ntab})
     traffic, traffic_src = None, None
@@ -761,8 +761,11 @@ def main():
         roofline = roofline_for(dom, k_s, (k_s * (dcnt if dom != "msm_fixed_kernel" else 1)) / (step_ms * 1e-3), s, c, sm_mhz)
         roofline["chosen_by"] = "largest per-kernel device time of a profiled step (kernels_ms_per_proof below)"
         r0 = sum(p["sc_cubic_round0_kernel"] for p in profs) / len(profs)
-        roofline["hbm_kernel_sample"] = {"kernel": "sc_cubic_kernel<false> (round 0: 4 tables x 32 B x 2^%d read)" % s,
-                                         "achieved": 4 * 32 * n / r0 / 1e9 if r0 > 0 else 0.0, "unit": "GB/s", "kernel_ms": 1e3 * r0}
+        # round 0 of phase one reads Az, Bz, Cz once (eq(tau) is factored out of the round polynomial: kernels.cu sc_cubic_eq_kernel)
+        roofline["hbm_kernel_sample"] = {"kernel": "sc_cubic_eq_kernel<false> (round 0: 3 tables x 32 B x 2^%d read; 4 F_l products per pair)" % s,
+                                         "achieved": 3 * 32 * n / r0 / 1e9 if r0 > 0 else 0.0, "unit": "GB/s", "kernel_ms": 1e3 * r0,
+                                         "int_pipe_frac": (4 * (n / 2) * 89 / r0) / int_pipe_peak(sm_mhz) if r0 > 0 else 0.0,
+                                         "note": "bound by the integer pipe (89 IMAD.WIDE per F_l product), not by HBM"}
 
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:

@@ -153,3 +153,19 @@ def test_sharded_witness_exchange(world, case, tmp_path):
     for env in (None, {"SB200_P2P": "0"}):
         for r in _run_sharded(world, case, tmp_path, env):
             assert r[16:] == want
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world,s,tail", [(2, 13, None), (4, 14, "0"), (2, 14, "6"), (8, 16, None)])
+def test_sharded_factored_first_sumcheck(world, s, tail, tmp_path):
+    """Every device round of phase one through the factored kernel (SB200_SC_LAT_PAIRS=0; kernels.cu sc_cubic_eq_kernel):
+    each rank's suffix eq tables carry the factor of the index bits its rank fixes, the per-rank (q(0), leading coefficient)
+    pairs are summed before the host rebuilds s(0), s(2), s(3).  Same bytes as the oracle."""
+    n = 1 << s
+    oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x0771)
+    want = O.nizk_prove(oi, ov, oin, O.Gens(n, n, 10), LABEL, TAPE_SEED, 8)
+    env = {"SB200_SC_LAT_PAIRS": "0"}
+    if tail is not None:
+        env["SB200_HOST_TAIL_LOG"] = tail
+    for r in _run_sharded(world, "syn:%d" % s, tmp_path, env):
+        assert r[16:] == want
