@@ -41,6 +41,17 @@ int sb200_k_eval_table_abc(const sb200_instance* inst, const uint8_t* rx_evals, 
 int sb200_k_sumcheck_round(uint8_t* const* tables, int ntab, size_t len, const uint8_t* r, uint8_t* evals3);
 /* DensePolynomial::bound: Z has n scalars viewed as Ls x (n/Ls); out n/Ls    dense_mlpoly.rs:205-212 */
 int sb200_k_poly_bound(const uint8_t* Z, size_t n, const uint8_t* Lv, size_t Ls, uint8_t* out);
+/* The same DensePolynomial::bound for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * UNLIKE the hooks of this header, d_Z (n scalars), d_L (Ls scalars) and d_out (n/Ls scalars) are DEVICE pointers of the
+ * caller, 16-byte aligned, Montgomery limbs as above; the two kernels are enqueued on `stream` (a cudaStream_t, NULL = the
+ * default stream) and the call returns without synchronising.  It calls no cudaMalloc / cudaFree or other allocating
+ * routine: the per-chunk partial sums live in a fixed 8 MiB array in the library's device image (held by every GPU that
+ * loads the library until the process exits), whose address is looked up once per device on the first call there.
+ * Limit: n / Ls <= 4096 columns (any Ls; n < 2^32) -- larger shapes get SB200_ERR_ARG and a message naming the limit.
+ * Every call on a device shares that array: calls that overlap on the GPU race and must be serialised by the caller.
+ * Nothing in it needs clearing between calls.  Output bytes equal sb200_k_poly_bound's. */
+int sb200_poly_bound_noalloc(const void* d_Z, size_t n, const void* d_L, size_t Ls, void* d_out, void* stream);
 /* DotProductProofLog::compute_dotproduct, n <= 65536                        nizk/mod.rs:430-433 */
 int sb200_k_dot(const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out);
 /* DensePolynomial::commit_inner: L rows of n/L canonical scalars, blinds canonical; out L x 32
