@@ -1411,39 +1411,65 @@ __global__ void __launch_bounds__(256, 2) msm_fixed_kernel(const niels_t* __rest
 // kept out of the row kernel so that the commitment can start before the RandomTape has produced the blinds),
 // and compresses.  One warp per row: the windows of blind*h and the partials are spread over the lanes and summed
 // by the quad tree, so the chain in front of the compression is ~25 field multiplications instead of 7 per window.
-static constexpr int kFinishWarps = 4;
-__global__ void __launch_bounds__(32 * kFinishWarps) msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit,
-                                                                      uint8_t* __restrict__ out32, const niels_t* __restrict__ tbl, uint32_t c,
-                                                                      uint32_t windows, const fl_t* __restrict__ extra_h, uint32_t h_index) {
-  const uint32_t lane = threadIdx.x & 31, row = blockIdx.x * kFinishWarps + (threadIdx.x >> 5);
-  if (row >= rows) return;  // whole warps
-  const uint32_t nh = extra_h != nullptr ? windows : 0, items = nh + nsplit;
-  ge_t acc = ge_identity();
-  if (lane < nh) {
-    const size_t epb = (size_t)windows << (c - 1);
-    uint32_t kw[8];
-    const uint4* q = reinterpret_cast<const uint4*>(extra_h + row);
-    uint4 a = __ldg(q), b = __ldg(q + 1);
-    kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
-    for (uint32_t w = lane; w < nh; w += 32) {
-      int32_t d = msm_digit_at(kw, w, c);
-      if (d != 0) {
-        bool neg = d < 0;
-        niels_t e = ldg_niels(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(neg ? -d : d) - 1));
-        acc = ge_madd_call(acc, e, neg);
+// The compression is a chain of ~280 dependent F_p products that costs a warp the same with one active lane as with 32,
+// so the W row sums of a block meet in shared memory and ONE warp compresses them, a row per lane: with 2048 rows the
+// chip runs 128 such chains side by side instead of 2048 (3.5 per SM sub-partition, each slowing the others down).
+// W grows with the row count so that the blocks stay at about one per SM (finish_warps()).
+template <int W>
+__global__ void __launch_bounds__(32 * W) msm_finish_kernel(const ge_t* __restrict__ partial, uint32_t rows, uint32_t nsplit,
+                                                            uint8_t* __restrict__ out32, const niels_t* __restrict__ tbl, uint32_t c,
+                                                            uint32_t windows, const fl_t* __restrict__ extra_h, uint32_t h_index) {
+  __shared__ ge_t srow[W];
+  const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5, row = blockIdx.x * W + wid;
+  if (row < rows) {  // whole warps
+    const uint32_t nh = extra_h != nullptr ? windows : 0, items = nh + nsplit;
+    ge_t acc = ge_identity();
+    if (lane < nh) {
+      const size_t epb = (size_t)windows << (c - 1);
+      uint32_t kw[8];
+      const uint4* q = reinterpret_cast<const uint4*>(extra_h + row);
+      uint4 a = __ldg(q), b = __ldg(q + 1);
+      kw[0] = a.x; kw[1] = a.y; kw[2] = a.z; kw[3] = a.w; kw[4] = b.x; kw[5] = b.y; kw[6] = b.z; kw[7] = b.w;
+      for (uint32_t w = lane; w < nh; w += 32) {
+        int32_t d = msm_digit_at(kw, w, c);
+        if (d != 0) {
+          bool neg = d < 0;
+          niels_t e = ldg_niels(tbl + (size_t)h_index * epb + ((size_t)w << (c - 1)) + ((uint32_t)(neg ? -d : d) - 1));
+          acc = ge_madd_call(acc, e, neg);
+        }
       }
     }
+    // item i (windows first, then the partials) belongs to lane i mod 32
+    for (uint32_t i = nh + ((lane + 32 - (nh & 31)) & 31); i < items; i += 32) acc = ge_add_call(acc, partial[(size_t)row * nsplit + (i - nh)]);
+    acc = warp_sum_ge_n(acc, items < 32 ? items : 32);
+    if (lane == 0) srow[wid] = acc;
   }
-  // item i (windows first, then the partials) belongs to lane i mod 32
-  for (uint32_t i = nh + ((lane + 32 - (nh & 31)) & 31); i < items; i += 32) acc = ge_add_call(acc, partial[(size_t)row * nsplit + (i - nh)]);
-  acc = warp_sum_ge_n(acc, items < 32 ? items : 32);
+  __syncthreads();
+  // co-resident blocks (b and b + 148 under round-robin placement) pick different warps, i.e. different sub-partitions
+  const uint32_t cw = (blockIdx.x / kSMs) % W;
+  if (wid != cw || lane >= W) return;
+  const uint32_t crow = blockIdx.x * W + lane;
+  if (crow >= rows) return;
   uint32_t w[8];
-  ge_compress_t<FpSqrInl>(acc, w);
-  if (lane == 0) {
-    uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)row * 32);
-    o[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    o[1] = make_uint4(w[4], w[5], w[6], w[7]);
-  }
+  ge_compress_t<FpSqrInl>(srow[lane], w);
+  uint4* o = reinterpret_cast<uint4*>(out32 + (size_t)crow * 32);
+  o[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  o[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+// warps (= rows) per block of msm_finish_kernel: 4 up to 592 rows, then 8, then 16.  SB200_FINISH_WARPS overrides.
+static int finish_warps(uint32_t rows) {
+  static const int forced = [] { const char* e = getenv("SB200_FINISH_WARPS"); int v = e ? atoi(e) : 0; return v == 4 || v == 8 || v == 16 ? v : 0; }();
+  if (forced) return forced;
+  return rows <= 4u * kSMs ? 4 : rows <= 8u * kSMs ? 8 : 16;
+}
+static cudaError_t launch_msm_finish(const ge_t* partial, uint32_t rows, uint32_t nsplit, uint8_t* out32, const niels_t* tbl, uint32_t c,
+                                     uint32_t windows, const fl_t* extra_h, uint32_t h_index, cudaStream_t s) {
+  const int W = finish_warps(rows);
+  KProf kp_("msm_finish_kernel", s);
+  if (W == 4) msm_finish_kernel<4><<<(rows + 3) / 4, 128, 0, s>>>(partial, rows, nsplit, out32, tbl, c, windows, extra_h, h_index);
+  else if (W == 8) msm_finish_kernel<8><<<(rows + 7) / 8, 256, 0, s>>>(partial, rows, nsplit, out32, tbl, c, windows, extra_h, h_index);
+  else msm_finish_kernel<16><<<(rows + 15) / 16, 512, 0, s>>>(partial, rows, nsplit, out32, tbl, c, windows, extra_h, h_index);
+  return cudaSuccess;
 }
 MsmPlan msm_plan(uint32_t rows, uint32_t n) {
   MsmPlan p;
@@ -1479,8 +1505,7 @@ cudaError_t msm_fixed(const MsmTable& t, const fl_t* scalars, size_t stride, uin
   cudaError_t e = SB_LAUNCHED();
   if (ev) cudaEventRecord(ev[1], s);
   if (e != cudaSuccess) return e;
-  { KProf kp_("msm_finish_kernel", s); msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
-      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, nullptr, 0); }
+  launch_msm_finish(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, nullptr, 0, s);
   return SB_LAUNCHED();
 }
 // The same in two halves: the row sums first (no blinds needed), then blind*h + compression.
@@ -1511,8 +1536,7 @@ cudaError_t msm_fixed_finish(const MsmTable& t, uint32_t rows, uint32_t n, const
                              uint8_t* out32, cudaStream_t s) {
   if (!rows) return cudaSuccess;
   MsmPlan p = msm_plan(rows, n);
-  { KProf kp_("msm_finish_kernel", s); msm_finish_kernel<<<(rows + kFinishWarps - 1) / kFinishWarps, 32 * kFinishWarps, 0, s>>>(
-      reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, extra_h, h_index); }
+  launch_msm_finish(reinterpret_cast<const ge_t*>(scratch), rows, p.splits, out32, t.tbl, t.c, t.windows, extra_h, h_index, s);
   return SB_LAUNCHED();
 }
 
