@@ -143,6 +143,9 @@ bool sc_round_is_long(size_t pairs, const ScWork& w);
 cudaError_t k_eq_pyramid(const fl_t* tau, uint32_t m, uint32_t lo_bits, fl_t init, fl_t* lo, fl_t* hi, cudaStream_t s);
 cudaError_t k_sc_cubic_eq(const fl_t* lo, const fl_t* hi, uint32_t lo_bits, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do_bind,
                           fl_t r, const ScWork& w, cudaStream_t s);
+// phase two on a z whose upper half is zero past its k0 leading entries (kernels.cu sc_quad_half0_kernel)
+cudaError_t k_sc_quad_half0(const fl_t* Z, const fl_t* Q, size_t h, uint32_t k0, const ScWork& w, cudaStream_t s);
+cudaError_t k_sc_half_fix(fl_t* Z, fl_t* Q, size_t h, uint32_t k0, fl_t t, cudaStream_t s);
 cudaError_t k_sc_quad(fl_t* Z, fl_t* Q, size_t n_old, bool do_bind, fl_t r, const ScWork& w, cudaStream_t s);
 
 // LZ[i] = sum_j Lv[j] * Z[j*R + i]                                    (dense_mlpoly.rs:205-212)

@@ -543,6 +543,40 @@ __global__ void __launch_bounds__(256, 2) sc_quad_kernel(fl_t* __restrict__ Z, f
   }
   grid_sum_fl<3>(e, smem, partials, counter, result, mb);
 }
+// ---- phase two, first round on a z whose upper half is almost empty ---------------------------------------------------
+// z = (w, 1, io, 0, ..., 0) (r1csproof.rs:150-160): of the upper half only the first k0 = 1 + |io| entries can be non-zero,
+// and the same holds for the combined table (rA A + rB B + rC C)^T eq(rx), whose columns past the inputs have no entries.
+// For a pair i >= k0 the round polynomial's value at 2 is (2*0 - z_i)(2*0 - q_i) = z_i q_i, its value at 0: one product and
+// two reads instead of two and four.  Binding r_0 then gives z'_i = (1 - r_0) z_i for i >= k0: the prover keeps the factor
+// outside the tables (prover.inc HalfZero) instead of running the bind, after sc_half_fix_kernel has put the k0 leading
+// entries on the same scale.
+template <class M>
+__global__ void __launch_bounds__(256, 2) sc_quad_half0_kernel(const fl_t* __restrict__ Z, const fl_t* __restrict__ Q, size_t h, uint32_t k0,
+                                                            fl_t* partials, unsigned int* counter, fl_t* result, Mailbox mb) {
+  __shared__ fl_t smem[3 * 32];
+  fl_t e[3];
+  e[0] = e[1] = e[2] = fl_zero();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < h; i += (size_t)gridDim.x * blockDim.x) {
+    const fl_t zl = ld_fl(Z + i), ql = ld_fl(Q + i);
+    const fl_t p = M::mul(zl, ql);  // sumcheck.rs:459-467
+    e[0] = fl_add(e[0], p);
+    if (i < k0) {
+      const fl_t zh = ld_fl(Z + i + h), qh = ld_fl(Q + i + h);
+      e[1] = fl_add(e[1], M::mul(fl_sub(fl_add(zh, zh), zl), fl_sub(fl_add(qh, qh), ql)));
+    } else {
+      e[1] = fl_add(e[1], p);
+    }
+  }
+  grid_sum_fl<3>(e, smem, partials, counter, result, mb);
+}
+// X[i] += t * X[i + h] for i < k0, both tables: with t = r/(1-r) the lower half times (1-r) is the table bound at r
+__global__ void sc_half_fix_kernel(fl_t* __restrict__ Z, fl_t* __restrict__ Q, size_t h, uint32_t k0, fl_t t) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * k0; i += gridDim.x * blockDim.x) {
+    fl_t* X = (i & 1) ? Q : Z;
+    const uint32_t k = i >> 1;
+    st_fl(X + k, fl_add(ld_fl(X + k), fl_mul_call(t, ld_fl(X + k + h))));
+  }
+}
 // ---- phase one with eq(tau) factored out of the round polynomial ------------------------------------------------------
 // Round j of prove_cubic_with_additive_term (sumcheck.rs:618-674) sums T*(A*B - C) over the table halves with
 // T = eq(tau) bound at r_0..r_{j-1}.  T is a product: T[b*h + x] = S_j * eq(tau_j, b) * E_j[x], S_j = prod_k eq(tau_k, r_k)
@@ -794,6 +828,19 @@ cudaError_t k_sc_cubic(fl_t* T, fl_t* A, fl_t* B, fl_t* C, size_t n_old, bool do
   else if (do_bind) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<true, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else if (compact) { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlCall><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
   else { KProf kp_("sc_cubic_kernel", s); sc_cubic_kernel<false, FlInl><<<g, 256, 0, s>>>(T, A, B, C, newlen, r, w.partials, w.counter, w.result, mb); }
+  return SB_LAUNCHED();
+}
+// round 0 of phase two over tables of 2h entries whose upper halves are zero from index k0 on (sc_quad_half0_kernel)
+cudaError_t k_sc_quad_half0(const fl_t* Z, const fl_t* Q, size_t h, uint32_t k0, const ScWork& w, cudaStream_t s) {
+  unsigned g = sc_grid(h, w);
+  Mailbox mb{w.host_result, w.host_flag, w.seq};
+  if (g <= compact_blocks()) { KProf kp_("sc_quad_half0_kernel", s); sc_quad_half0_kernel<FlCall><<<g, 256, 0, s>>>(Z, Q, h, k0, w.partials, w.counter, w.result, mb); }
+  else { KProf kp_("sc_quad_half0_kernel", s); sc_quad_half0_kernel<FlInl><<<g, 256, 0, s>>>(Z, Q, h, k0, w.partials, w.counter, w.result, mb); }
+  return SB_LAUNCHED();
+}
+cudaError_t k_sc_half_fix(fl_t* Z, fl_t* Q, size_t h, uint32_t k0, fl_t t, cudaStream_t s) {
+  if (!k0) return cudaSuccess;
+  { KProf kp_("sc_half_fix_kernel", s); sc_half_fix_kernel<<<(2 * k0 + 127) / 128, 128, 0, s>>>(Z, Q, h, k0, t); }
   return SB_LAUNCHED();
 }
 // rounds with this many pairs run sc_cubic_kernel / sc_quad_kernel (the others the four-lane latency variants)

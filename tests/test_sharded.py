@@ -164,7 +164,7 @@ def test_sharded_factored_first_sumcheck(world, s, tail, tmp_path):
     n = 1 << s
     oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x0771)
     want = O.nizk_prove(oi, ov, oin, O.Gens(n, n, 10), LABEL, TAPE_SEED, 8)
-    env = {"SB200_SC_LAT_PAIRS": "0"}
+    env = {"SB200_SC_LAT_PAIRS": "0", "SB200_SC_HALF_ZERO": "2"}  # and phase two's half-empty z from the first size on
     if tail is not None:
         env["SB200_HOST_TAIL_LOG"] = tail
     for r in _run_sharded(world, "syn:%d" % s, tmp_path, env):
