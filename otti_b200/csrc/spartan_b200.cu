@@ -396,45 +396,54 @@ int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint6
   rc = ensure_device();
   if (rc) return rc;
   const uint64_t size_z = num_vars + num_inputs + 1;
-  FlVec Z(size_z);
-  uint64_t st = seed;
-  for (uint64_t i = 0; i < size_z; i++) {  // Scalar::random = from_u512(8 x next_u64), ristretto255.rs:381-387
-    uint8_t wide[64];
-    for (int k = 0; k < 8; k++) {
-      uint64_t w = splitmix64(st);
-      memcpy(wide + 8 * k, &w, 8);
+  // Every loop below runs in slices on the ingestion threads: SplitMix64's state after k draws is seed + k * increment, so a
+  // slice starts its stream where the sequential generator would be; the inverses come from one inversion per slice.
+  FlVec Z(size_z), Zinv(size_z);
+  const unsigned T = ingest_threads(size_z);
+  run_threads(T, [&](unsigned t) {
+    const uint64_t i0 = size_z * t / T, i1 = size_z * (t + 1) / T;
+    uint64_t st = seed + 8 * i0 * 0x9E3779B97F4A7C15ULL;
+    for (uint64_t i = i0; i < i1; i++) {  // Scalar::random = from_u512(8 x next_u64), ristretto255.rs:381-387
+      uint8_t wide[64];
+      for (int k = 0; k < 8; k++) {
+        uint64_t w = splitmix64(st);
+        memcpy(wide + 8 * k, &w, 8);
+      }
+      Z[i] = fl_from_bytes_wide(wide);
     }
-    Z[i] = fl_from_bytes_wide(wide);
-  }
-  Z[num_vars] = fl_one();
-  // Z^-1 for the C coefficients with one shared inversion
-  FlVec pre(size_z), Zinv(size_z);
-  Fl acc = fl_one();
-  for (uint64_t i = 0; i < size_z; i++) {
-    pre[i] = acc;
-    if (!Z[i].is_zero()) acc = fl_mul(acc, Z[i]);
-  }
-  acc = fl_invert(acc);
-  for (uint64_t i = size_z; i-- > 0;) {
-    if (Z[i].is_zero()) { Zinv[i] = fl_zero(); continue; }
-    Zinv[i] = fl_mul(acc, pre[i]);
-    acc = fl_mul(acc, Z[i]);
-  }
+    if (num_vars >= i0 && num_vars < i1) Z[num_vars] = fl_one();
+    // Z^-1 for the C coefficients with one shared inversion per slice
+    FlVec pre(i1 - i0);
+    Fl acc = fl_one();
+    for (uint64_t i = i0; i < i1; i++) {
+      pre[i - i0] = acc;
+      if (!Z[i].is_zero()) acc = fl_mul(acc, Z[i]);
+    }
+    acc = fl_invert(acc);
+    for (uint64_t i = i1; i-- > i0;) {
+      if (Z[i].is_zero()) { Zinv[i] = fl_zero(); continue; }
+      Zinv[i] = fl_mul(acc, pre[i - i0]);
+      acc = fl_mul(acc, Z[i]);
+    }
+  });
   CooHost M[3];
   FlVec V[3];
   for (int m = 0; m < 3; m++) {
     M[m].nnz = num_cons;
     M[m].rows.resize(num_cons); M[m].cols.resize(num_cons); V[m].resize(num_cons);
   }
-  for (uint64_t i = 0; i < num_cons; i++) {
-    uint64_t ai = i % size_z, bi = (i + 2) % size_z, ci = (i + 3) % size_z;
-    for (int m = 0; m < 3; m++) M[m].rows[i] = (uint32_t)i;
-    M[0].cols[i] = (uint32_t)ai; V[0][i] = fl_one();
-    M[1].cols[i] = (uint32_t)bi; V[1][i] = fl_one();
-    Fl ab = fl_mul(Z[ai], Z[bi]);
-    if (Z[ci].is_zero()) { M[2].cols[i] = (uint32_t)num_vars; V[2][i] = ab; }
-    else { M[2].cols[i] = (uint32_t)ci; V[2][i] = fl_mul(ab, Zinv[ci]); }
-  }
+  const unsigned Tc = ingest_threads(num_cons);
+  run_threads(Tc, [&](unsigned t) {
+    for (uint64_t i = num_cons * t / Tc, e = num_cons * (t + 1) / Tc; i < e; i++) {
+      uint64_t ai = i % size_z, bi = (i + 2) % size_z, ci = (i + 3) % size_z;
+      for (int m = 0; m < 3; m++) M[m].rows[i] = (uint32_t)i;
+      M[0].cols[i] = (uint32_t)ai; V[0][i] = fl_one();
+      M[1].cols[i] = (uint32_t)bi; V[1][i] = fl_one();
+      Fl ab = fl_mul(Z[ai], Z[bi]);
+      if (Z[ci].is_zero()) { M[2].cols[i] = (uint32_t)num_vars; V[2][i] = ab; }
+      else { M[2].cols[i] = (uint32_t)ci; V[2][i] = fl_mul(ab, Zinv[ci]); }
+    }
+  });
   for (int m = 0; m < 3; m++) M[m].mont = V[m].data();
   Instance* inst = new Instance();
   inst->num_cons = num_cons; inst->num_vars = num_vars; inst->num_inputs = num_inputs;
@@ -443,7 +452,9 @@ int sb200_instance_synthetic_sharded(uint64_t num_cons, uint64_t num_vars, uint6
   uint32_t bad_scalar[3];
   rc = upload_sparse(M, num_cons, 2 * num_vars, *inst, bad_scalar);
   if (rc) { delete inst; return rc; }
-  for (uint64_t i = 0; i < num_vars; i++) fl_to_bytes(Z[i], vars32_out + 32 * i);
+  run_threads(T, [&](unsigned t) {
+    for (uint64_t i = num_vars * t / T, e = num_vars * (t + 1) / T; i < e; i++) fl_to_bytes(Z[i], vars32_out + 32 * i);
+  });
   for (uint64_t i = 0; i < num_inputs; i++) fl_to_bytes(Z[num_vars + 1 + i], inputs32_out + 32 * i);
   *out = reinterpret_cast<sb200_instance*>(inst);
   return SB200_OK;
