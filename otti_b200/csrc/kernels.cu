@@ -1693,9 +1693,12 @@ static uint32_t msm_small_threads() {
 }
 uint32_t msm_small_blocks(uint32_t rows, uint32_t n, uint32_t windows) {
   uint32_t pairs = n * windows;
-  const uint32_t per_block = 2 * msm_small_threads();
+  // SB200_MSM_SMALL_UNITS (experiment knob): (term, window) units per thread, default 2; SB200_MSM_SMALL_CAP: blocks per SM, default 2
+  static const uint32_t upt = [] { const char* e = getenv("SB200_MSM_SMALL_UNITS"); int v = e ? atoi(e) : 2; return (uint32_t)(v >= 1 && v <= 16 ? v : 2); }();
+  static const uint32_t bps = [] { const char* e = getenv("SB200_MSM_SMALL_CAP"); int v = e ? atoi(e) : 2; return (uint32_t)(v >= 1 && v <= 4 ? v : 2); }();
+  const uint32_t per_block = upt * msm_small_threads();
   uint32_t want = (pairs + per_block - 1) / per_block;  // ~2 look-ups per thread
-  uint32_t cap = (uint32_t)(kSMs * 2) / (rows ? rows : 1);
+  uint32_t cap = (uint32_t)(kSMs * bps) / (rows ? rows : 1);
   if (cap < 1) cap = 1;
   if (want < 1) want = 1;
   return want < cap ? want : cap;
