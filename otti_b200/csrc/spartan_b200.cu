@@ -298,7 +298,7 @@ int sb200_instance_new_sharded(uint64_t num_cons, uint64_t num_vars, uint64_t nu
   int bad_code[3] = {0, 0, 0};
   bool any_bad = false;
   for (int m = 0; m < 3; m++) {
-    if (nnz[m] >= (1ull << 32)) return SB200_ERR_ARG;
+    if (nnz[m] >= (1ull << 31)) { set_error("more than 2^31 - 1 non-zero entries in one matrix"); return SB200_ERR_ARG; }  // the device sort counts in int
     M[m].nnz = nnz[m];
     M[m].canon = vals32[m];
     M[m].rows.resize(nnz[m]);
