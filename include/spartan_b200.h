@@ -22,7 +22,12 @@
  *    or C++ exception crosses the boundary.  sb200_last_error() gives the text
  *    for the calling thread;
  *  - there is NO CPU fallback: every compute entry point fails with
- *    SB200_ERR_NO_DEVICE when no sm_100 GPU is usable.
+ *    SB200_ERR_NO_DEVICE when no sm_100 GPU is usable;
+ *  - handles may be shared between threads, as the reference's `&Instance` / `&NIZKGens` are: every call that uses an
+ *    instance's device workspace (prove, verify, is_sat, witness upload, encode) holds that instance's mutex, and the two
+ *    provers also serialise on one process-wide mutex (one process drives one GPU, and its host worker pool has a single
+ *    posting thread).  Concurrent calls are therefore safe and run one after the other; freeing a handle while a call
+ *    on it is in flight is not.
  */
 #ifndef SPARTAN_B200_H
 #define SPARTAN_B200_H
