@@ -47,7 +47,7 @@ fi
 
 if has full; then
 # 5. full capture of the dominant kernels at 2^22 (one launch each)
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'msm_fixed_kernel|sc_cubic_kernel|sc_quad_kernel|spmvT3|spmv3' -c 14 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'msm_fixed_kernel|msm_finish_kernel|sc_cubic_eq_kernel|sc_cubic_kernel|sc_quad_half0_kernel|sc_quad_kernel|spmvT3|spmv3' -c 16 \
   -o $out/${tag}_full_2p22 -f python bench.py --steps 1 --warmup 1 --no-side --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 # the report itself is too large to travel (64 MiB limit of gpurun_out): keep the raw-page CSV and a per-kernel summary
