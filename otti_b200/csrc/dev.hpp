@@ -60,7 +60,7 @@ cudaError_t k_mail_tables(const fl_t* p0, const fl_t* p1, const fl_t* p2, const 
 
 // ---- F_l vector kernels -------------------------------------------------------------------
 // canonical -> Montgomery, flag[0] |= 1 if any input >= l            (lib.rs:65-89)
-cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s);
+cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s, fl_t* out2 = nullptr);  // out2: optional second copy
 cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s);
 // out[i] = a[i] op b[i]  (op 0 add, 1 sub, 2 mul) -- parity-test hook for the limb arithmetic
 cudaError_t k_fl_binop(int op, const fl_t* a, const fl_t* b, fl_t* out, size_t n, cudaStream_t s);

@@ -205,13 +205,16 @@ __device__ __forceinline__ void grid_sum_fl(fl_t (&x)[NV], fl_t* smem, fl_t* par
 }
 
 // ------------------------------------------------------------------ elementwise
-__global__ void to_mont_kernel(const fl_t* __restrict__ in, fl_t* __restrict__ out, size_t n, uint32_t* flag) {
+// out2 (optional): a second copy of the result -- the witness in Montgomery form and the lower half of z are the same values
+__global__ void to_mont_kernel(const fl_t* __restrict__ in, fl_t* __restrict__ out, fl_t* __restrict__ out2, size_t n, uint32_t* flag) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
   bool bad = false;
   for (; i < n; i += stride) {
     fl_t x = ldg_fl(in + i);
     bad |= !fl_is_canonical(x);
-    st_fl(out + i, fl_to_mont(x));
+    const fl_t m = fl_to_mont(x);
+    st_fl(out + i, m);
+    if (out2 != nullptr) st_fl(out2 + i, m);
   }
   if (bad) atomicOr(flag, 1u);
 }
@@ -244,9 +247,9 @@ cudaError_t k_fp_binop(int op, const fp_t* a, const fp_t* b, fp_t* out, size_t n
   { KProf kp_("fp_binop_kernel", s); fp_binop_kernel<<<grid_for(n, 128), 128, 0, s>>>(op, a, b, out, n); }
   return SB_LAUNCHED();
 }
-cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s) {
+cudaError_t k_to_mont(const fl_t* in, fl_t* out, size_t n, uint32_t* flag, cudaStream_t s, fl_t* out2) {
   if (!n) return cudaSuccess;
-  { KProf kp_("to_mont_kernel", s); to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, n, flag); }
+  { KProf kp_("to_mont_kernel", s); to_mont_kernel<<<grid_for(n, 256), 256, 0, s>>>(in, out, out2, n, flag); }
   return SB_LAUNCHED();
 }
 cudaError_t k_from_mont(const fl_t* in, fl_t* out, size_t n, cudaStream_t s) {
