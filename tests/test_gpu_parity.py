@@ -663,7 +663,8 @@ def test_full_size_properties(sb, s):
 
 @pytest.mark.parametrize("env", [{"SB200_SC_LAT_PAIRS": "0", "SB200_SC_HALF_ZERO": "2"},
                                  {"SB200_SC_LAT_PAIRS": "0", "SB200_SC_HALF_ZERO": "2", "SB200_HOST_TAIL_LOG": "0"},
-                                 {"SB200_SC_EQ_FACTOR": "0", "SB200_SC_HALF_ZERO": "1"}, {"SB200_SC_HALF_ZERO": "0"}])
+                                 {"SB200_SC_EQ_FACTOR": "0", "SB200_SC_HALF_ZERO": "1"}, {"SB200_SC_HALF_ZERO": "0"},
+                                 {"SB200_SC_LAT_PAIRS": "0", "SB200_SC_HALF_ZERO": "2", "SB200_SC_HALF_ZERO_FALLBACK": "1"}])
 def test_factored_first_sumcheck_gives_the_same_proof(env):
     """Phase one's long rounds run with eq(tau) factored out of the round polynomial (kernels.cu sc_cubic_eq_kernel,
     prover.inc EqFactor).  By default that covers the rounds above 8192 pairs (instances from 2^15 on, which the full-size
@@ -671,7 +672,8 @@ def test_factored_first_sumcheck_gives_the_same_proof(env):
     SB200_SC_EQ_FACTOR=0 switches it off: the proof bytes stay the oracle's (sumcheck.rs:618-674).  The same runs cover phase
     two's first rounds, which skip the (almost empty) upper half of z and keep the factor 1 - r_0 outside the tables
     (sc_quad_half0_kernel, prover.inc HalfZero; SB200_SC_HALF_ZERO = least pairs per rank, default 2^17, 0 = off) -- with 3, 10 and 100 inputs, and with the final
-    claims read from the device (SB200_HOST_TAIL_LOG=0) or from the host's tail rounds.  The variables are read once per
+    claims read from the device (SB200_HOST_TAIL_LOG=0) or from the host's tail rounds, and through the path kept for the
+    challenge r_0 = 1 (SB200_SC_HALF_ZERO_FALLBACK=1: the ordinary bind after clearing what was left unwritten).  The variables are read once per
     process, hence the subprocess."""
     import hashlib
     import os

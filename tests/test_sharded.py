@@ -156,7 +156,7 @@ def test_sharded_witness_exchange(world, case, tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,s,tail", [(2, 13, None), (4, 14, "0"), (2, 14, "6"), (8, 16, None)])
+@pytest.mark.parametrize("world,s,tail", [(2, 13, None), (4, 14, "0"), (2, 14, "6"), (8, 16, None), (4, 13, "fallback")])
 def test_sharded_factored_first_sumcheck(world, s, tail, tmp_path):
     """Every device round of phase one through the factored kernel (SB200_SC_LAT_PAIRS=0; kernels.cu sc_cubic_eq_kernel):
     each rank's suffix eq tables carry the factor of the index bits its rank fixes, the per-rank (q(0), leading coefficient)
@@ -165,7 +165,9 @@ def test_sharded_factored_first_sumcheck(world, s, tail, tmp_path):
     oi, ov, oin = O.Instance.synthetic(n, n, 10, 0x0771)
     want = O.nizk_prove(oi, ov, oin, O.Gens(n, n, 10), LABEL, TAPE_SEED, 8)
     env = {"SB200_SC_LAT_PAIRS": "0", "SB200_SC_HALF_ZERO": "2"}  # and phase two's half-empty z from the first size on
-    if tail is not None:
+    if tail == "fallback":
+        env["SB200_SC_HALF_ZERO_FALLBACK"] = "1"  # the path of the challenge r_0 = 1: ordinary bind over cleared upper halves
+    elif tail is not None:
         env["SB200_HOST_TAIL_LOG"] = tail
     for r in _run_sharded(world, "syn:%d" % s, tmp_path, env):
         assert r[16:] == want
