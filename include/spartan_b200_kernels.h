@@ -17,6 +17,9 @@
 extern "C" {
 #endif
 
+/* Scalar::invert of one canonical scalar on the HOST (no device needed): the inversion the prover's Fiat-Shamir tail uses
+ * (fermat = 0: extended Euclid) or a^(l-2) as the reference computes it (fermat != 0); 0 -> 0.    ristretto255.rs:548-602 */
+int sb200_k_host_invert(const uint8_t* in_canon, uint8_t* out_canon, int fermat);
 /* Scalar add / sub / mul (op 0/1/2), elementwise over n                 ristretto255.rs:702-755 */
 int sb200_k_fl_binop(int op, const uint8_t* a, const uint8_t* b, uint8_t* out, size_t n);
 /* Coordinate field F_p, p = 2^255-19 (curve25519-dalek FieldElement behind group.rs:6-7): out = canonical

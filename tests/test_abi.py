@@ -108,3 +108,26 @@ def test_keccak_variants_agree():
         outs.append(r.stdout.split())
     assert outs[0][0] == "d5a21972d0d5fe320c0d263fac7fffb8145aa640af6e9bca177c03c7efcf0615"
     assert outs[0] == outs[1]
+
+
+def test_host_inversion_matches_fermat_and_python():
+    """host/hfl.hpp fl_invert (binary extended Euclid with batched halvings) against a^(l-2) and Python's pow(x, -1, l): the
+    bullet rounds invert their challenge with it (nizk/bullet.rs:100-101, ristretto255.rs:548-602)."""
+    import ctypes as C
+    import random
+    import otti_b200
+    L = otti_b200.lib()
+    ell = 2 ** 252 + 27742317777372353535851937790883648493
+    rng = random.Random(99)
+    xs = [0, 1, 2, 3, ell - 1, ell - 2, (ell + 1) // 2, 2 ** 64, 2 ** 128, 2 ** 192, 2 ** 252, 2 ** 252 - 1, 2 ** 63, 2 ** 126 + 1]
+    xs += [1 << k for k in range(0, 252, 7)] + [(1 << k) - 1 for k in range(2, 252, 11)]
+    xs += [rng.randrange(ell) for _ in range(3000)] + [rng.randrange(1 << rng.randrange(1, 252)) for _ in range(500)]
+    out = (C.c_uint8 * 32)()
+    for x in xs:
+        b = (C.c_uint8 * 32).from_buffer_copy(x.to_bytes(32, "little"))
+        want = pow(x, -1, ell) if x else 0
+        for fermat in (0, 1):
+            assert L.sb200_k_host_invert(b, out, fermat) == 0
+            assert int.from_bytes(bytes(out), "little") == want, (x, fermat)
+    bad = (C.c_uint8 * 32).from_buffer_copy(ell.to_bytes(32, "little"))
+    assert L.sb200_k_host_invert(bad, out, 0) == -5
